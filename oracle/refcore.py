@@ -34,3 +34,28 @@ def load_hooks():
             sys.path.insert(0, p)
     load()
     return importlib.import_module("magritte.ref_hooks")
+
+
+class TraceHook:
+    """numpy-facing wrapper of ref_hooks.TraceHook (arrays travel as raw bytes)."""
+
+    def __init__(self, model):
+        import numpy as np
+        self._np = np
+        self._h = load_hooks().TraceHook(model)
+        self.length = self._h.length()
+        self.centre = self._h.centre()
+
+    def trace(self, o, rr, l):
+        np = self._np
+        d = dict(self._h.trace(int(o), int(rr), int(l)))
+        for k in ("nr", "nr_interp"):
+            d[k] = np.frombuffer(d[k], dtype=np.uint32).copy()
+        for k in ("interp_factor", "shift", "dZ"):
+            d[k] = np.frombuffer(d[k], dtype=np.float64).copy()
+        return d
+
+
+def dshift_max(model):
+    import numpy as np
+    return np.frombuffer(load_hooks().dshift_max(model), dtype=np.float64).copy()
