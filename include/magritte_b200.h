@@ -1,0 +1,162 @@
+/*
+ * magritte_b200.h -- C ABI of libmagritte_b200.so: the B200 implementation of Magritte's
+ * Feautrier order-2 formal-solver hot path.
+ *
+ * This is the drop-in boundary. The reference has no FFI layer of its own
+ * for this path: `Solver` is a header-only template struct instantiated inside
+ * src/model/model.cpp:353-390 and reached from Python through
+ * src/bindings/pybindings.cpp:185 (`compute_radiation_field_feautrier_order_2`). The entry points
+ * below are what a `Model` method would bind instead of constructing that `Solver`; every one
+ * cites the reference code it replaces. Plain pointers and sizes only; all pointers are HOST
+ * pointers unless a name ends in `_dev`. Every function returns 0 on success and a negative
+ * MGB_E* code on failure; mgb_last_error() then describes the failure. There is no CPU fallback:
+ * without a CUDA device mgb_create() fails.
+ *
+ * Array layouts are the reference's (row-major Paracabs Matrix/Tensor,
+ * dependencies/Paracabs/Paracabs/datatypes/matrix.hpp:74, tensor.hpp:77; Vector3D = 3 doubles).
+ */
+#ifndef MAGRITTE_B200_H
+#define MAGRITTE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MGB_ABI_VERSION 1
+
+enum { MGB_OK = 0, MGB_EINVAL = -1, MGB_ECUDA = -2, MGB_ESTATE = -3, MGB_ENOMEM = -4, MGB_EUNSUPPORTED = -5, MGB_ENCCL = -6 };
+
+/* ApproximationType of the reference (src/solver/solver.hpp: enum ApproximationType {None, OneLine, CloseLines});
+ * chosen by Model::compute_radiation_field_feautrier_order_2 from the parameters (model.cpp:366-389). */
+enum { MGB_APPROX_NONE = 0, MGB_APPROX_ONELINE = 1, MGB_APPROX_CLOSELINES = 2 };
+
+/* BoundaryCondition (src/model/geometry/boundary/boundary.hpp: enum BoundaryCondition {Zero, Thermal, CMB}). */
+enum { MGB_BC_ZERO = 0, MGB_BC_THERMAL = 1, MGB_BC_CMB = 2 };
+
+typedef struct mgb_ctx mgb_ctx;
+
+/* The tunables of Parameters that the path reads (src/model/parameters/parameters.hpp:66-124). */
+typedef struct mgb_params {
+    double min_opacity;                       /* parameters.hpp: min_opacity = 1e-26 */
+    double max_distance_opacity_contribution; /* = 10 (CloseLines window, solver.tpp:1219) */
+    double max_interpolation_diff;            /* = 1.4 (sub-step criterion, solver_interp_helper.tpp:68) */
+    double max_width_fraction;                /* = 0.35 (Model::set_dshift_max, model.cpp:1158-1178) */
+    uint32_t n_off_diag;                      /* = 0; >0 not yet supported (MGB_EUNSUPPORTED) */
+    uint32_t store_intensities;               /* keep u(rr,o,f) (Radiation::u, solver.tpp:461-465,503) */
+    /* implementation knobs (no reference counterpart) */
+    uint64_t path_cache_bytes;                /* HBM budget for cached ray paths; 0 = library default */
+    uint64_t scratch_bytes;                   /* HBM budget for per-chunk u/Lambda scratch; 0 = default */
+    uint32_t cache_paths;                     /* 1: keep traced paths across calls when they fit the budget */
+    uint32_t reserved;
+} mgb_params;
+
+/* Work and timing counters of the last mgb_run_feautrier_order_2 (Sigma S, Sigma D, Sigma N). */
+typedef struct mgb_stats {
+    uint64_t n_steps;        /* Sigma S: geometric ray steps (valid get_next results), both directions */
+    uint64_t n_nbs_scanned;  /* Sigma D: neighbours inspected by get_next */
+    uint64_t n_entries;      /* Sigma N: ray entries summed over (o, rr, line) (sub-steps included) */
+    uint64_t n_solves;       /* (o, rr, f) tridiagonal systems solved */
+    uint64_t n_large_shift;  /* segments x frequencies that took the line-integrated (erff) branch */
+    uint32_t max_ray_length; /* longest geometric half-ray pair (steps) */
+    uint32_t n_chunks;       /* origin chunks the call was split into */
+    uint32_t n_launches;     /* kernels launched by the call */
+    uint32_t paths_cached;   /* 1 if the trace was served from the path cache */
+    float ms_trace_count;    /* device time, CUDA events on the launching stream */
+    float ms_trace_fill;
+    float ms_solve;          /* the dominant kernel: eta/chi + two-sided Thomas sweep */
+    float ms_reduce;         /* J and Lambda accumulation in reference order */
+    float ms_total;          /* first launch to last completion */
+    uint32_t n_solve_launches;
+    uint32_t reserved;
+} mgb_stats;
+
+/* ---- life cycle ----------------------------------------------------------------------------- */
+int mgb_abi_version(void);
+/* Create a context on CUDA device `device` (cudaSetDevice). Replaces the per-call `Solver solver;`
+ * of model.cpp:356 and Paracabs' accelerator state. Fails with MGB_ECUDA when there is no device. */
+int mgb_create(int device, mgb_ctx** out);
+void mgb_destroy(mgb_ctx* ctx);
+const char* mgb_last_error(const mgb_ctx* ctx); /* ctx may be NULL: error of the last failed mgb_create */
+
+/* ---- model upload (the device mirrors of src/model/{geometry,thermodynamics,lines,radiation}) -- */
+/* Geometry: points.position/velocity (points.hpp), CSR neighbour lists n_neighbors/neighbors
+ * (points.hpp:15-17; cum_n_neighbors is rebuilt here), rays.direction/weight/antipod (rays.hpp),
+ * boundary.point2boundary / boundary_condition / boundary_temperature (boundary.hpp).
+ * velocity is v/c as in the reference. point2boundary[p] == npoints marks an interior point. */
+int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* position, const double* velocity,
+                     const uint32_t* n_neighbors, const uint32_t* neighbors, uint64_t n_neighbors_total,
+                     uint32_t nrays, const double* direction, const double* weight, const uint32_t* antipod,
+                     uint32_t nboundary, const uint32_t* point2boundary, const int32_t* boundary_condition,
+                     const double* boundary_temperature, int spherical_symmetry);
+/* thermodynamics.temperature.gas, thermodynamics.turbulence.vturb2 (both [npoints]). */
+int mgb_set_thermodynamics(mgb_ctx* ctx, const double* temperature_gas, const double* vturb2);
+/* Static line tables (Lines::read, src/model/lines/lines.cpp:11-69): per species nrad and
+ * linedata.inverse_mass; per line (species-major order, lid = nrad_cum[lspec] + k) the centre
+ * frequency lines.line and Einstein A; quadrature.weights [nlspecs][nquads]. The sorted line list
+ * of lines.cpp:52-64 is rebuilt inside. */
+int mgb_set_lines(mgb_ctx* ctx, uint32_t nlspecs, const uint32_t* nrad, const double* inverse_mass,
+                  const double* line, const double* einstein_A, uint32_t nquads, const double* quadrature_weights);
+/* radiation.frequencies.nu [npoints][nfreqs] with f = lid*nquads + z (Model::compute_spectral_discretisation,
+ * model.cpp:70-161) and corresponding_line [nfreqs] (frequencies.hpp:13-22; only read by OneLine). */
+int mgb_set_frequencies(mgb_ctx* ctx, uint32_t nfreqs, const double* nu, const uint32_t* corresponding_line);
+/* Per-iteration line state: lines.emissivity / opacity / inverse_width [npoints][nlines]
+ * (Lines::set_emissivity_and_opacity, lines.tpp:29-41; set_inverse_width, :45-59) and
+ * lineProducingSpecies[l].population_tot [nlspecs][npoints]. Also derives the InterpHelper criterion
+ * (solver_interp_helper.hpp:15-30) and Model::dshift_max (model.cpp:1158-1178) on the device. */
+int mgb_set_line_state(mgb_ctx* ctx, const double* emissivity, const double* opacity, const double* inverse_width,
+                       const double* population_tot);
+int mgb_params_default(mgb_params* p);
+int mgb_set_params(mgb_ctx* ctx, const mgb_params* p);
+
+/* ---- the hot path --------------------------------------------------------------------------- */
+/* Solver::setup + Solver::solve_feautrier_order_2<approx>(Model&) (solver.tpp:1-13, 458-540) for origins
+ * o in [o_begin, o_end) and all hnrays ray pairs: trace, eta/chi, Feautrier order-2 solve, J and Lambda
+ * accumulation, results left in device memory. Synchronous. `stats` may be NULL. */
+int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats);
+/* Copy results of the last run to the host. J: rows [o_begin,o_end) of radiation.J, (o_end-o_begin)*nfreqs.
+ * Lambda (n_off_diag = 0: the diagonal operator): lambda_val [(o_end-o_begin)][nlines] holds Ls for the
+ * element (p=o, k, nr=o) that Lambda::add_element accumulated (lambda.tpp:79-89), lambda_cnt the list
+ * length (0 or 1). u: radiation.u rows, [hnrays][(o_end-o_begin)][nfreqs], only if store_intensities. */
+int mgb_get_J(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J);
+int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* lambda_val, uint32_t* lambda_cnt);
+int mgb_get_u(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* u);
+/* One call, host buffers in and out (what Model::compute_radiation_field_feautrier_order_2 binds):
+ * mgb_set_line_state + mgb_run + mgb_get_J + mgb_get_lambda (+ mgb_get_u if u != NULL). */
+int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const double* emissivity, const double* opacity,
+                                const double* inverse_width, const double* population_tot, uint32_t o_begin,
+                                uint32_t o_end, double* J, double* lambda_val, uint32_t* lambda_cnt, double* u,
+                                mgb_stats* stats);
+/* Device addresses of the result buffers (full-size [npoints][nfreqs] / [npoints][nlines]) for in-place
+ * collectives: replaces Radiation::MPI_reduce_J / Lambda::MPI_gather (radiation.cpp:76-91, lambda.tpp:121-206). */
+int mgb_result_ptrs_dev(mgb_ctx* ctx, void** J_dev, void** lambda_val_dev, void** lambda_cnt_dev);
+/* Drop cached ray paths (geometry unchanged): the next run traces again. */
+int mgb_invalidate_paths(mgb_ctx* ctx);
+
+/* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
+/* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */
+int mgb_nccl_unique_id(void* id128);
+int mgb_comm_init(mgb_ctx* ctx, int nranks, int rank, const void* id128);
+/* Even split of [0,npoints) into nranks contiguous ranges of equal element count (the last padded). */
+int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end);
+/* In-place ncclAllGather of the J and Lambda slices every rank computed for its mgb_partition range. */
+int mgb_allgather_results(mgb_ctx* ctx);
+
+/* ---- test hooks ------------------------------------------------------------------------------ */
+/* The ray of (origin o, ray pair rr, line l) exactly as Solver::trace_ray_for_line fills nr_/nr_interp_/
+ * interp_factor_/shift_/dZ_ between first_ and last_ (solver.tpp:484-496, 773-800, 1057-1097).
+ * Arrays have capacity `cap`; returns n_tot in *n_out and the centre's offset from first_ in *centre_out. */
+int mgb_trace_dump(mgb_ctx* ctx, uint32_t o, uint32_t rr, uint32_t l, uint32_t cap, uint32_t* nr, uint32_t* nr_interp,
+                   double* interp_factor, double* shift, double* dZ, uint32_t* n_out, uint32_t* centre_out);
+/* Device libm self-test: evaluates fn (0 expf, 1 logf, 2 erff, 3 expm1f, 4 powf) on n host-supplied
+ * inputs (y only for powf) with the device implementation; the caller compares with its own libm. */
+int mgb_selftest_libm(mgb_ctx* ctx, int fn, uint64_t n, const float* x, const float* y, float* out);
+/* Sustained DFMA rate of the device in TFLOP/s (2 flops per DFMA): the FP64 roofline denominator. */
+int mgb_measure_fp64_peak(mgb_ctx* ctx, double* tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MAGRITTE_B200_H */

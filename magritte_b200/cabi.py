@@ -1,0 +1,252 @@
+"""ctypes binding of libmagritte_b200.so (the C ABI declared in include/magritte_b200.h).
+
+This is the Python-side stub a maintainer of the reference would add next to
+`magritte.core`; the library itself has no Python or torch dependency.
+There is no CPU fallback: loading fails loudly if the shared library has not been built, and
+`Context()` raises if there is no CUDA device.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmagritte_b200.so")
+
+EXPORTS = [
+    "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
+    "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
+    "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
+    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition",
+    "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak",
+]
+
+
+class Params(C.Structure):
+    _fields_ = [("min_opacity", C.c_double), ("max_distance_opacity_contribution", C.c_double),
+                ("max_interpolation_diff", C.c_double), ("max_width_fraction", C.c_double),
+                ("n_off_diag", C.c_uint32), ("store_intensities", C.c_uint32),
+                ("path_cache_bytes", C.c_uint64), ("scratch_bytes", C.c_uint64),
+                ("cache_paths", C.c_uint32), ("reserved", C.c_uint32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("n_steps", C.c_uint64), ("n_nbs_scanned", C.c_uint64), ("n_entries", C.c_uint64),
+                ("n_solves", C.c_uint64), ("n_large_shift", C.c_uint64), ("max_ray_length", C.c_uint32),
+                ("n_chunks", C.c_uint32), ("n_launches", C.c_uint32), ("paths_cached", C.c_uint32),
+                ("ms_trace_count", C.c_float), ("ms_trace_fill", C.c_float), ("ms_solve", C.c_float),
+                ("ms_reduce", C.c_float), ("ms_total", C.c_float), ("n_solve_launches", C.c_uint32),
+                ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (fails loudly when it has not been built: no fallback)."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} not built: run magritte_b200/csrc/build.sh (or __graft_entry__.build())")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.mgb_last_error.restype = C.c_char_p
+        _lib.mgb_last_error.argtypes = [C.c_void_p]
+        _lib.mgb_destroy.restype = None
+        _lib.mgb_destroy.argtypes = [C.c_void_p]
+    return _lib
+
+
+class MgbError(RuntimeError):
+    pass
+
+
+def _p(a, dtype):
+    a = np.ascontiguousarray(a, dtype=dtype)
+    return a, a.ctypes.data_as(C.c_void_p)
+
+
+class Context:
+    """Owns one mgb_ctx. All arrays are host numpy arrays in the reference's layouts."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        self._ctx = C.c_void_p()
+        rc = self.lib.mgb_create(C.c_int(device), C.byref(self._ctx))
+        if rc != 0:
+            raise MgbError(f"mgb_create failed ({rc}): {self.lib.mgb_last_error(None).decode()}")
+        self.params = Params()
+        self.lib.mgb_params_default(C.byref(self.params))
+        self.npoints = self.nfreqs = self.nlines = self.hnrays = 0
+        self._keep = {}
+
+    def close(self):
+        if self._ctx:
+            self.lib.mgb_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise MgbError(f"{what} failed ({rc}): {self.lib.mgb_last_error(self._ctx).decode()}")
+
+    # ---- upload -----------------------------------------------------------------------------
+    def set_params(self, **kw):
+        for k, v in kw.items():
+            if not hasattr(self.params, k):
+                raise KeyError(k)
+            setattr(self.params, k, v)
+        self._check(self.lib.mgb_set_params(self._ctx, C.byref(self.params)), "mgb_set_params")
+
+    def set_model(self, flat):
+        """Upload everything from a `flatten.flatten_model` dict."""
+        f = flat
+        self.npoints, self.nlines, self.nfreqs = int(f["npoints"]), int(f["nlines"]), int(f["nfreqs"])
+        self.hnrays, self.nrays = int(f["hnrays"]), int(f["nrays"])
+        prm = f["params"]
+        self.set_params(min_opacity=prm["min_opacity"],
+                        max_distance_opacity_contribution=prm["max_distance_opacity_contribution"],
+                        max_interpolation_diff=prm["max_interpolation_diff"], max_width_fraction=prm["max_width_fraction"],
+                        n_off_diag=int(prm["n_off_diag"]))
+        pos, ppos = _p(f["position"], np.float64)
+        vel, pvel = _p(f["velocity"], np.float64)
+        nn, pnn = _p(f["n_neighbors"], np.uint32)
+        nb, pnb = _p(f["neighbors"], np.uint32)
+        d, pd = _p(f["direction"], np.float64)
+        w, pw = _p(f["weight"], np.float64)
+        ap, pap = _p(f["antipod"], np.uint32)
+        p2b, pp2b = _p(f["point2boundary"], np.uint32)
+        bc, pbc = _p(f["boundary_condition"], np.int32)
+        bt, pbt = _p(f["boundary_temperature"], np.float64)
+        self._check(self.lib.mgb_set_geometry(self._ctx, C.c_uint32(self.npoints), ppos, pvel, pnn, pnb,
+                                              C.c_uint64(int(nn.sum(dtype=np.uint64))), C.c_uint32(self.nrays), pd, pw, pap,
+                                              C.c_uint32(int(f["nboundary"])), pp2b, pbc, pbt,
+                                              C.c_int(int(f["spherical_symmetry"]))), "mgb_set_geometry")
+        T, pT = _p(f["temperature"], np.float64)
+        vt, pvt = _p(f["vturb2"], np.float64)
+        self._check(self.lib.mgb_set_thermodynamics(self._ctx, pT, pvt), "mgb_set_thermodynamics")
+        nrad, pnrad = _p(f["nrad"], np.uint32)
+        im, pim = _p(f["inverse_mass"], np.float64)
+        ln, pln = _p(f["line"], np.float64)
+        A, pA = _p(f["line_A"], np.float64)
+        qw, pqw = _p(f["quad_weights"], np.float64)
+        self._check(self.lib.mgb_set_lines(self._ctx, C.c_uint32(int(f["nlspecs"])), pnrad, pim, pln, pA,
+                                           C.c_uint32(int(f["nquads"])), pqw), "mgb_set_lines")
+        nu, pnu = _p(f["nu"], np.float64)
+        cl, pcl = _p(f["corresponding_line"], np.uint32)
+        self._check(self.lib.mgb_set_frequencies(self._ctx, C.c_uint32(self.nfreqs), pnu, pcl), "mgb_set_frequencies")
+        self.set_line_state(f["emissivity"], f["opacity"], f["inverse_width"], f["population_tot"])
+
+    def set_line_state(self, emissivity, opacity, inverse_width, population_tot):
+        e, pe = _p(emissivity, np.float64)
+        o, po = _p(opacity, np.float64)
+        w, pw = _p(inverse_width, np.float64)
+        t, pt = _p(population_tot, np.float64)
+        self._check(self.lib.mgb_set_line_state(self._ctx, pe, po, pw, pt), "mgb_set_line_state")
+
+    # ---- run --------------------------------------------------------------------------------
+    def run(self, approx=2, o_range=None):
+        o0, o1 = o_range or (0, self.npoints)
+        st = Stats()
+        self._check(self.lib.mgb_run_feautrier_order_2(self._ctx, C.c_int(approx), C.c_uint32(o0), C.c_uint32(o1),
+                                                       C.byref(st)), "mgb_run_feautrier_order_2")
+        self.last_range = (o0, o1)
+        return st
+
+    def get_J(self, o_range=None):
+        o0, o1 = o_range or self.last_range
+        J = np.empty((o1 - o0, self.nfreqs))
+        self._check(self.lib.mgb_get_J(self._ctx, C.c_uint32(o0), C.c_uint32(o1), J.ctypes.data_as(C.c_void_p)), "mgb_get_J")
+        return J
+
+    def get_lambda(self, o_range=None):
+        o0, o1 = o_range or self.last_range
+        val = np.empty((o1 - o0, self.nlines))
+        cnt = np.empty((o1 - o0, self.nlines), dtype=np.uint32)
+        self._check(self.lib.mgb_get_lambda(self._ctx, C.c_uint32(o0), C.c_uint32(o1), val.ctypes.data_as(C.c_void_p),
+                                            cnt.ctypes.data_as(C.c_void_p)), "mgb_get_lambda")
+        return val, cnt
+
+    def get_u(self):
+        o0, o1 = self.last_range
+        u = np.empty((self.hnrays, o1 - o0, self.nfreqs))
+        self._check(self.lib.mgb_get_u(self._ctx, C.c_uint32(o0), C.c_uint32(o1), u.ctypes.data_as(C.c_void_p)), "mgb_get_u")
+        return u
+
+    def solve(self, emissivity, opacity, inverse_width, population_tot, approx=2, o_range=None, J=None, lam=None):
+        """mgb_solve_feautrier_order_2: host buffers in, host buffers out (the end-to-end call)."""
+        o0, o1 = o_range or (0, self.npoints)
+        e, pe = _p(emissivity, np.float64)
+        o, po = _p(opacity, np.float64)
+        w, pw = _p(inverse_width, np.float64)
+        t, pt = _p(population_tot, np.float64)
+        if J is None:
+            J = np.empty((o1 - o0, self.nfreqs))
+        if lam is None:
+            lam = (np.empty((o1 - o0, self.nlines)), np.empty((o1 - o0, self.nlines), dtype=np.uint32))
+        st = Stats()
+        self._check(self.lib.mgb_solve_feautrier_order_2(
+            self._ctx, C.c_int(approx), pe, po, pw, pt, C.c_uint32(o0), C.c_uint32(o1), J.ctypes.data_as(C.c_void_p),
+            lam[0].ctypes.data_as(C.c_void_p), lam[1].ctypes.data_as(C.c_void_p), None, C.byref(st)),
+            "mgb_solve_feautrier_order_2")
+        self.last_range = (o0, o1)
+        return J, lam, st
+
+    def invalidate_paths(self):
+        self._check(self.lib.mgb_invalidate_paths(self._ctx), "mgb_invalidate_paths")
+
+    # ---- multi-GPU --------------------------------------------------------------------------
+    def nccl_unique_id(self):
+        buf = (C.c_char * 128)()
+        rc = self.lib.mgb_nccl_unique_id(buf)
+        if rc != 0:
+            raise MgbError("mgb_nccl_unique_id failed")
+        return bytes(buf)
+
+    def comm_init(self, nranks, rank, uid):
+        self._check(self.lib.mgb_comm_init(self._ctx, C.c_int(nranks), C.c_int(rank), C.c_char_p(uid)), "mgb_comm_init")
+
+    def partition(self, nranks, rank):
+        a, b = C.c_uint32(), C.c_uint32()
+        self._check(self.lib.mgb_partition(self._ctx, C.c_int(nranks), C.c_int(rank), C.byref(a), C.byref(b)), "mgb_partition")
+        return a.value, b.value
+
+    def allgather(self):
+        self._check(self.lib.mgb_allgather_results(self._ctx), "mgb_allgather_results")
+        self.last_range = (0, self.npoints)
+
+    # ---- test hooks -------------------------------------------------------------------------
+    def trace(self, o, rr, l, cap=4096):
+        nr, nri = np.zeros(cap, np.uint32), np.zeros(cap, np.uint32)
+        fac, sh, dz = np.zeros(cap), np.zeros(cap), np.zeros(cap)
+        n, c = C.c_uint32(), C.c_uint32()
+        self._check(self.lib.mgb_trace_dump(self._ctx, C.c_uint32(o), C.c_uint32(rr), C.c_uint32(l), C.c_uint32(cap),
+                                            nr.ctypes.data_as(C.c_void_p), nri.ctypes.data_as(C.c_void_p),
+                                            fac.ctypes.data_as(C.c_void_p), sh.ctypes.data_as(C.c_void_p),
+                                            dz.ctypes.data_as(C.c_void_p), C.byref(n), C.byref(c)), "mgb_trace_dump")
+        k = n.value
+        return dict(nr=nr[:k], nr_interp=nri[:k], interp_factor=fac[:k], shift=sh[:k], dZ=dz[:max(k - 1, 0)],
+                    centre_offset=c.value, n_tot=k)
+
+    def libm(self, fn, x, y=None):
+        x, px = _p(x, np.float32)
+        out = np.empty_like(x)
+        py = None
+        if y is not None:
+            y, py = _p(y, np.float32)
+        code = {"expf": 0, "logf": 1, "erff": 2, "expm1f": 3, "powf": 4}[fn]
+        self._check(self.lib.mgb_selftest_libm(self._ctx, C.c_int(code), C.c_uint64(x.size), px, py,
+                                               out.ctypes.data_as(C.c_void_p)), "mgb_selftest_libm")
+        return out
+
+    def fp64_peak_tflops(self):
+        v = C.c_double()
+        self._check(self.lib.mgb_measure_fp64_peak(self._ctx, C.byref(v)), "mgb_measure_fp64_peak")
+        return v.value

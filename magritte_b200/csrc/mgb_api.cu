@@ -1,0 +1,531 @@
+// mgb_api.cu -- C ABI of libmagritte_b200.so: context, model upload, the Feautrier order-2 run, result download.
+// See include/magritte_b200.h for the contract and the reference citations of every entry point.
+#include <algorithm>
+#include <numeric>
+
+#include <cub/device/device_scan.cuh>
+
+#include "mgb_ctx.h"
+#include "mgb_solve.cuh"
+
+using namespace mgb;
+
+static std::string g_create_error;
+
+mgb_ctx::~mgb_ctx() {
+    drop_chunks();
+    if (stream) cudaStreamDestroy(stream);
+}
+
+static int upload(mgb_ctx* ctx, DevBuf& b, const void* host, size_t bytes) {
+    MGB_CUDA(ctx, b.ensure(bytes));
+    if (bytes) MGB_CUDA(ctx, cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return MGB_OK;
+}
+#define MGB_TRY(x)            \
+    do {                      \
+        int rc_ = (x);        \
+        if (rc_ != MGB_OK) return rc_; \
+    } while (0)
+
+extern "C" int mgb_abi_version(void) { return MGB_ABI_VERSION; }
+
+extern "C" int mgb_params_default(mgb_params* p) {
+    if (!p) return MGB_EINVAL;
+    memset(p, 0, sizeof *p);
+    p->min_opacity                       = 1.0e-26;
+    p->max_distance_opacity_contribution = 10.0;
+    p->max_interpolation_diff            = 1.4;
+    p->max_width_fraction                = 0.35;
+    p->n_off_diag                        = 0;
+    p->store_intensities                 = 0;
+    p->path_cache_bytes                  = 48ull << 30;
+    p->scratch_bytes                     = 8ull << 30;
+    p->cache_paths                       = 1;
+    return MGB_OK;
+}
+
+extern "C" int mgb_create(int device, mgb_ctx** out) {
+    if (!out) return MGB_EINVAL;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0) {
+        g_create_error = std::string("no CUDA device: ") + cudaGetErrorString(e) + " (libmagritte_b200 has no CPU fallback)";
+        return MGB_ECUDA;
+    }
+    if (device < 0 || device >= ndev) { g_create_error = "device index out of range"; return MGB_EINVAL; }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) { g_create_error = cudaGetErrorString(e); return MGB_ECUDA; }
+    mgb_ctx* ctx = new mgb_ctx();
+    ctx->device  = device;
+    if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        g_create_error = cudaGetErrorString(e);
+        delete ctx;
+        return MGB_ECUDA;
+    }
+    mgb_params defaults;
+    mgb_params_default(&defaults);
+    mgb_set_params(ctx, &defaults);
+    *out = ctx;
+    return MGB_OK;
+}
+
+extern "C" void mgb_destroy(mgb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    delete ctx;
+}
+
+extern "C" const char* mgb_last_error(const mgb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+extern "C" int mgb_set_params(mgb_ctx* ctx, const mgb_params* p) {
+    if (!ctx || !p) return MGB_EINVAL;
+    if (p->n_off_diag != 0) return ctx->fail(MGB_EUNSUPPORTED, "n_off_diag > 0 (banded Lambda operator) is not implemented");
+    if (p->max_width_fraction != ctx->params.max_width_fraction) ctx->points_dirty = true;
+    ctx->params = *p;
+    if (ctx->params.path_cache_bytes == 0) ctx->params.path_cache_bytes = 48ull << 30;
+    if (ctx->params.scratch_bytes == 0) ctx->params.scratch_bytes = 8ull << 30;
+    ctx->m.min_opacity = p->min_opacity;
+    ctx->m.max_dist    = p->max_distance_opacity_contribution;
+    ctx->m.log_max_interp_diff = (double)logf((float)p->max_interpolation_diff); /* logf(double) as in solver_interp_helper.tpp:68 */
+    return MGB_OK;
+}
+
+extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* position, const double* velocity,
+                                const uint32_t* n_neighbors, const uint32_t* neighbors, uint64_t n_neighbors_total,
+                                uint32_t nrays, const double* direction, const double* weight, const uint32_t* antipod,
+                                uint32_t nboundary, const uint32_t* point2boundary, const int32_t* boundary_condition,
+                                const double* boundary_temperature, int spherical_symmetry) {
+    if (!ctx) return MGB_EINVAL;
+    if (!npoints || !position || !velocity || !n_neighbors || !neighbors || !nrays || (nrays & 1) || !direction || !weight ||
+        !antipod || !point2boundary || (nboundary && (!boundary_condition || !boundary_temperature)))
+        return ctx->fail(MGB_EINVAL, "mgb_set_geometry: null or inconsistent argument");
+    cudaSetDevice(ctx->device);
+    std::vector<double4> p4(npoints), v4(npoints);
+    std::vector<uint2> csr(npoints);
+    uint64_t cum = 0;
+    for (uint32_t i = 0; i < npoints; i++) {
+        p4[i] = make_double4(position[3 * i], position[3 * i + 1], position[3 * i + 2], 0.0);
+        v4[i] = make_double4(velocity[3 * i], velocity[3 * i + 1], velocity[3 * i + 2], 0.0);
+        csr[i] = make_uint2((uint32_t)cum, n_neighbors[i]);
+        cum += n_neighbors[i];
+    }
+    if (cum != n_neighbors_total) return ctx->fail(MGB_EINVAL, "mgb_set_geometry: sum(n_neighbors) = %llu != n_neighbors_total = %llu",
+                                                   (unsigned long long)cum, (unsigned long long)n_neighbors_total);
+    if (cum > 0xffffffffull) return ctx->fail(MGB_EINVAL, "mgb_set_geometry: neighbour list exceeds 2^32 entries");
+    for (uint64_t i = 0; i < cum; i++)
+        if (neighbors[i] >= npoints) return ctx->fail(MGB_EINVAL, "mgb_set_geometry: neighbour index out of range");
+    for (uint32_t r = 0; r < nrays; r++)
+        if (antipod[r] >= nrays) return ctx->fail(MGB_EINVAL, "mgb_set_geometry: antipod index out of range");
+    MGB_TRY(upload(ctx, ctx->pos, p4.data(), sizeof(double4) * npoints));
+    MGB_TRY(upload(ctx, ctx->vel, v4.data(), sizeof(double4) * npoints));
+    MGB_TRY(upload(ctx, ctx->csr, csr.data(), sizeof(uint2) * npoints));
+    MGB_TRY(upload(ctx, ctx->nbs, neighbors, sizeof(uint32_t) * cum));
+    MGB_TRY(upload(ctx, ctx->dir, direction, sizeof(double) * 3 * nrays));
+    MGB_TRY(upload(ctx, ctx->weight, weight, sizeof(double) * nrays));
+    MGB_TRY(upload(ctx, ctx->antipod, antipod, sizeof(uint32_t) * nrays));
+    MGB_TRY(upload(ctx, ctx->p2b, point2boundary, sizeof(uint32_t) * npoints));
+    MGB_TRY(upload(ctx, ctx->bcond, boundary_condition, sizeof(int32_t) * nboundary));
+    MGB_TRY(upload(ctx, ctx->btemp, boundary_temperature, sizeof(double) * nboundary));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); /* host vectors go out of scope */
+    DevModel& m = ctx->m;
+    m.npoints = npoints; m.nrays = nrays; m.hnrays = nrays / 2; m.nboundary = nboundary; m.spherical = spherical_symmetry ? 1 : 0;
+    m.pos = ctx->pos.as<double4>(); m.vel = ctx->vel.as<double4>(); m.csr = ctx->csr.as<uint2>(); m.nbs = ctx->nbs.as<uint32_t>();
+    m.dir = ctx->dir.as<double>(); m.weight = ctx->weight.as<double>(); m.antipod = ctx->antipod.as<uint32_t>();
+    m.p2b = ctx->p2b.as<uint32_t>(); m.bcond = ctx->bcond.as<int32_t>(); m.btemp = ctx->btemp.as<double>();
+    ctx->have_geometry = true;
+    ctx->have_thermo = ctx->have_freqs = ctx->have_state = false; /* sized by npoints */
+    ctx->lens_o0 = ctx->lens_o1 = 0;
+    ctx->drop_chunks();
+    ctx->points_dirty = true;
+    return MGB_OK;
+}
+
+extern "C" int mgb_set_thermodynamics(mgb_ctx* ctx, const double* temperature_gas, const double* vturb2) {
+    if (!ctx) return MGB_EINVAL;
+    if (!ctx->have_geometry) return ctx->fail(MGB_ESTATE, "mgb_set_thermodynamics before mgb_set_geometry");
+    if (!temperature_gas || !vturb2) return ctx->fail(MGB_EINVAL, "mgb_set_thermodynamics: null argument");
+    cudaSetDevice(ctx->device);
+    const size_t n = ctx->m.npoints;
+    MGB_TRY(upload(ctx, ctx->temperature, temperature_gas, 8 * n));
+    MGB_TRY(upload(ctx, ctx->vturb2, vturb2, 8 * n));
+    MGB_CUDA(ctx, ctx->sqrtw_max.ensure(8 * n));
+    MGB_CUDA(ctx, ctx->dshift_max.ensure(8 * n));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->m.temperature = ctx->temperature.as<double>(); ctx->m.vturb2 = ctx->vturb2.as<double>();
+    ctx->m.sqrtw_max = ctx->sqrtw_max.as<double>(); ctx->m.dshift_max = ctx->dshift_max.as<double>();
+    ctx->have_thermo  = true;
+    ctx->points_dirty = true;
+    return MGB_OK;
+}
+
+extern "C" int mgb_set_lines(mgb_ctx* ctx, uint32_t nlspecs, const uint32_t* nrad, const double* inverse_mass, const double* line,
+                             const double* einstein_A, uint32_t nquads, const double* quadrature_weights) {
+    if (!ctx) return MGB_EINVAL;
+    if (!nlspecs || !nrad || !inverse_mass || !line || !einstein_A || !nquads || !quadrature_weights)
+        return ctx->fail(MGB_EINVAL, "mgb_set_lines: null or zero argument");
+    cudaSetDevice(ctx->device);
+    ctx->nrad.assign(nrad, nrad + nlspecs);
+    ctx->inverse_mass.assign(inverse_mass, inverse_mass + nlspecs);
+    ctx->nrad_cum.assign(nlspecs, 0);
+    uint32_t nlines = 0;
+    for (uint32_t l = 0; l < nlspecs; l++) { ctx->nrad_cum[l] = nlines; nlines += nrad[l]; }
+    if (!nlines) return ctx->fail(MGB_EINVAL, "mgb_set_lines: no lines");
+    ctx->line_spec.resize(nlines); ctx->line_k.resize(nlines);
+    std::vector<double> linv(nlines), lquad((size_t)nlines * nquads);
+    // max_inverse_mass: Lines::read starts from 0 and keeps the largest species value (lines.cpp:40-46)
+    ctx->max_inverse_mass = 0.0;
+    for (uint32_t l = 0; l < nlspecs; l++) {
+        if (inverse_mass[l] > ctx->max_inverse_mass) ctx->max_inverse_mass = inverse_mass[l];
+        for (uint32_t k = 0; k < nrad[l]; k++) {
+            const uint32_t lid = ctx->nrad_cum[l] + k;
+            ctx->line_spec[lid] = l; ctx->line_k[lid] = k; linv[lid] = inverse_mass[l];
+            for (uint32_t z = 0; z < nquads; z++) lquad[(size_t)lid * nquads + z] = quadrature_weights[(size_t)l * nquads + z];
+        }
+    }
+    // sorted line list + index map (lines.cpp:52-64, heapsort with index tracking; stable order for distinct centres)
+    std::vector<uint32_t> smap(nlines);
+    std::iota(smap.begin(), smap.end(), 0u);
+    std::stable_sort(smap.begin(), smap.end(), [&](uint32_t a, uint32_t b) { return line[a] < line[b]; });
+    std::vector<double> sline(nlines);
+    for (uint32_t i = 0; i < nlines; i++) sline[i] = line[smap[i]];
+    MGB_TRY(upload(ctx, ctx->line, line, 8 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->line_A, einstein_A, 8 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->sorted_line, sline.data(), 8 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->sorted_map, smap.data(), 4 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->line_invmass, linv.data(), 8 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->line_k_dev, ctx->line_k.data(), 4 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->line_spec_dev, ctx->line_spec.data(), 4 * (size_t)nlines));
+    MGB_TRY(upload(ctx, ctx->line_quadw, lquad.data(), 8 * lquad.size()));
+    MGB_TRY(upload(ctx, ctx->inv_mass_dev, inverse_mass, 8 * (size_t)nlspecs));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    DevModel& m = ctx->m;
+    m.nlines = nlines; m.nlspecs = nlspecs; m.nquads = nquads;
+    m.line = ctx->line.as<double>(); m.line_A = ctx->line_A.as<double>(); m.sorted_line = ctx->sorted_line.as<double>();
+    m.sorted_map = ctx->sorted_map.as<uint32_t>(); m.line_invmass = ctx->line_invmass.as<double>();
+    m.line_k = ctx->line_k_dev.as<uint32_t>(); m.line_quadw = ctx->line_quadw.as<double>();
+    ctx->have_lines = true;
+    ctx->have_state = ctx->have_freqs = false;
+    ctx->points_dirty = true;
+    return MGB_OK;
+}
+
+extern "C" int mgb_set_frequencies(mgb_ctx* ctx, uint32_t nfreqs, const double* nu, const uint32_t* corresponding_line) {
+    if (!ctx) return MGB_EINVAL;
+    if (!ctx->have_geometry || !ctx->have_lines) return ctx->fail(MGB_ESTATE, "mgb_set_frequencies before geometry/lines");
+    if (!nu || !corresponding_line) return ctx->fail(MGB_EINVAL, "mgb_set_frequencies: null argument");
+    if (nfreqs != ctx->m.nlines * ctx->m.nquads)
+        return ctx->fail(MGB_EINVAL, "mgb_set_frequencies: nfreqs = %u but nlines*nquads = %u (the solver needs the line discretisation "
+                                     "of Model::compute_spectral_discretisation())", nfreqs, ctx->m.nlines * ctx->m.nquads);
+    cudaSetDevice(ctx->device);
+    MGB_TRY(upload(ctx, ctx->nu, nu, 8 * (size_t)ctx->m.npoints * nfreqs));
+    MGB_TRY(upload(ctx, ctx->corr_line, corresponding_line, 4 * (size_t)nfreqs));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->m.nfreqs = nfreqs; ctx->m.nu = ctx->nu.as<double>(); ctx->m.corr_line = ctx->corr_line.as<uint32_t>();
+    ctx->have_freqs = true;
+    return MGB_OK;
+}
+
+extern "C" int mgb_set_line_state(mgb_ctx* ctx, const double* emissivity, const double* opacity, const double* inverse_width,
+                                  const double* population_tot) {
+    if (!ctx) return MGB_EINVAL;
+    if (!ctx->have_geometry || !ctx->have_lines) return ctx->fail(MGB_ESTATE, "mgb_set_line_state before geometry/lines");
+    if (!emissivity || !opacity || !inverse_width || !population_tot) return ctx->fail(MGB_EINVAL, "mgb_set_line_state: null argument");
+    cudaSetDevice(ctx->device);
+    const DevModel& m = ctx->m;
+    const size_t n    = (size_t)m.npoints * m.nlines;
+    MGB_TRY(upload(ctx, ctx->stage_a, emissivity, 8 * n));
+    MGB_TRY(upload(ctx, ctx->stage_b, opacity, 8 * n));
+    MGB_TRY(upload(ctx, ctx->stage_c, inverse_width, 8 * n));
+    MGB_TRY(upload(ctx, ctx->stage_d, population_tot, 8 * (size_t)m.nlspecs * m.npoints));
+    MGB_CUDA(ctx, ctx->lrow.ensure(sizeof(LineRow) * n));
+    k_prepare_rows<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(m.npoints, m.nlines, ctx->stage_a.as<double>(),
+                                                                         ctx->stage_b.as<double>(), ctx->stage_c.as<double>(),
+                                                                         ctx->stage_d.as<double>(), ctx->line_spec_dev.as<uint32_t>(),
+                                                                         ctx->lrow.as<LineRow>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->m.lrow     = ctx->lrow.as<LineRow>();
+    ctx->have_state = true;
+    // the sub-step counts depend on the criterion, the geometric paths do not: cached paths stay valid
+    return MGB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The run
+// ---------------------------------------------------------------------------------------------------
+namespace {
+
+struct EventTimer {
+    cudaEvent_t a = nullptr, b = nullptr;
+    cudaStream_t s;
+    explicit EventTimer(cudaStream_t st) : s(st) { cudaEventCreate(&a); cudaEventCreate(&b); }
+    ~EventTimer() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    void start() { cudaEventRecord(a, s); }
+    float stop() { /* synchronising: the run is synchronous anyway */
+        cudaEventRecord(b, s);
+        cudaEventSynchronize(b);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, a, b);
+        return ms;
+    }
+};
+
+int refresh_points(mgb_ctx* ctx) {
+    if (!ctx->points_dirty) return MGB_OK;
+    const DevModel& m = ctx->m;
+    k_prepare_points<<<(m.npoints + 255) / 256, 256, 0, ctx->stream>>>(m.npoints, m.nlspecs, m.temperature, m.vturb2,
+                                                                      ctx->inv_mass_dev.as<double>(), ctx->max_inverse_mass,
+                                                                      ctx->params.max_width_fraction, ctx->sqrtw_max.as<double>(),
+                                                                      ctx->dshift_max.as<double>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    ctx->points_dirty = false;
+    return MGB_OK;
+}
+
+// Count pass: geometric length of every half-ray of origins [o0,o1) (once per geometry and range).
+int ensure_lens(mgb_ctx* ctx, uint32_t o0, uint32_t o1, mgb_stats* st, uint32_t& launches) {
+    const DevModel& m = ctx->m;
+    if (ctx->lens_o1 > ctx->lens_o0 && o0 >= ctx->lens_o0 && o1 <= ctx->lens_o1) return MGB_OK;
+    MGB_CUDA(ctx, ctx->lens.ensure(4 * (size_t)m.npoints * m.nrays));
+    MGB_CUDA(ctx, ctx->counters.ensure(8 * 8));
+    MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+    const uint32_t no = o1 - o0;
+    const size_t nw   = (size_t)no * m.nrays;
+    EventTimer t(ctx->stream);
+    t.start();
+    PathView pv{};
+    k_trace<false><<<(unsigned)((nw * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, o0, no, ctx->lens.as<uint32_t>(), pv,
+                                                                               ctx->counters.as<unsigned long long>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    MGB_CUDA(ctx, ctx->origin_tot.ensure(8 * (size_t)no));
+    k_origin_totals<<<(no + 255) / 256, 256, 0, ctx->stream>>>(o0, no, m.nrays, ctx->lens.as<uint32_t>(),
+                                                               ctx->origin_tot.as<unsigned long long>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    launches += 2;
+    const float ms = t.stop();
+    if (st) st->ms_trace_count += ms;
+    ctx->origin_steps.resize(no);
+    unsigned long long c[3];
+    MGB_CUDA(ctx, cudaMemcpy(ctx->origin_steps.data(), ctx->origin_tot.p, 8 * (size_t)no, cudaMemcpyDeviceToHost));
+    MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 24, cudaMemcpyDeviceToHost));
+    ctx->tot_steps = c[0]; ctx->tot_scanned = c[1]; ctx->max_len = (uint32_t)c[2];
+    ctx->lens_o0 = o0; ctx->lens_o1 = o1;
+    ctx->drop_chunks();
+    return MGB_OK;
+}
+
+int fill_chunk(mgb_ctx* ctx, PathChunk& ch, mgb_stats* st, uint32_t& launches) {
+    const DevModel& m = ctx->m;
+    const uint32_t no = ch.o1 - ch.o0;
+    const size_t nhr  = (size_t)no * m.nrays;
+    MGB_CUDA(ctx, ch.poff.ensure(8 * nhr));
+    MGB_CUDA(ctx, ch.shift0.ensure(8 * nhr));
+    MGB_CUDA(ctx, ch.nr.ensure(4 * (size_t)ch.steps));
+    MGB_CUDA(ctx, ch.dZ.ensure(8 * (size_t)ch.steps));
+    MGB_CUDA(ctx, ch.shift.ensure(8 * (size_t)ch.steps));
+    EventTimer t(ctx->stream);
+    t.start();
+    const uint32_t* lens_chunk = ctx->lens.as<uint32_t>() + (size_t)ch.o0 * m.nrays;
+    size_t tmp = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp, lens_chunk, ch.poff.as<unsigned long long>(), (int64_t)nhr, ctx->stream);
+    MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+    MGB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, lens_chunk, ch.poff.as<unsigned long long>(), (int64_t)nhr,
+                                                ctx->stream));
+    PathView pv{};
+    pv.o0 = ch.o0; pv.no = no; pv.len = ctx->lens.as<uint32_t>(); pv.poff = ch.poff.as<unsigned long long>();
+    pv.nr = ch.nr.as<uint32_t>(); pv.dZ = ch.dZ.as<double>(); pv.shift = ch.shift.as<double>(); pv.shift0 = ch.shift0.as<double>();
+    k_trace<true><<<(unsigned)((nhr * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, ch.o0, no, nullptr, pv, nullptr);
+    MGB_CUDA(ctx, cudaGetLastError());
+    launches += 2;
+    const float ms = t.stop();
+    if (st) st->ms_trace_fill += ms;
+    ch.filled = true;
+    return MGB_OK;
+}
+
+template <int APPROX>
+void launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
+    const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
+    const size_t blocks = (nitems * 32 + 127) / 128;
+    k_solve<APPROX><<<(unsigned)blocks, 128, 0, ctx->stream>>>(ctx->m, pv, sc, nchunks_f);
+}
+
+} // namespace
+
+extern "C" int mgb_invalidate_paths(mgb_ctx* ctx) {
+    if (!ctx) return MGB_EINVAL;
+    cudaSetDevice(ctx->device);
+    for (auto* c : ctx->chunks) c->filled = false;
+    ctx->work.filled = false;
+    return MGB_OK;
+}
+
+extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats) {
+    if (!ctx) return MGB_EINVAL;
+    if (!(ctx->have_geometry && ctx->have_thermo && ctx->have_lines && ctx->have_freqs && ctx->have_state))
+        return ctx->fail(MGB_ESTATE, "mgb_run_feautrier_order_2: model incomplete (geometry %d thermo %d lines %d freqs %d state %d)",
+                         ctx->have_geometry, ctx->have_thermo, ctx->have_lines, ctx->have_freqs, ctx->have_state);
+    if (approx < 0 || approx > 2) return ctx->fail(MGB_EINVAL, "approx must be 0 (None), 1 (OneLine) or 2 (CloseLines)");
+    DevModel& m = ctx->m;
+    if (o_begin >= o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "origin range [%u,%u) invalid for npoints = %u", o_begin, o_end, m.npoints);
+    if (ctx->params.n_off_diag) return ctx->fail(MGB_EUNSUPPORTED, "n_off_diag > 0 is not implemented");
+    cudaSetDevice(ctx->device);
+    mgb_stats st;
+    memset(&st, 0, sizeof st);
+    uint32_t launches = 0;
+    EventTimer total(ctx->stream);
+    total.start();
+    MGB_TRY(refresh_points(ctx));
+    MGB_TRY(ensure_lens(ctx, o_begin, o_end, &st, launches));
+
+    const uint32_t nchunks_f = (m.nfreqs + 31) / 32;
+    // ---- plan origin chunks: bounded scratch (16 B per solve) and bounded path bytes (20 B per step) ----
+    const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * 16;
+    const uint32_t max_o_scratch    = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / per_origin_scratch);
+    unsigned long long range_steps  = 0;
+    for (uint32_t o = o_begin; o < o_end; o++) range_steps += ctx->origin_steps[o - ctx->lens_o0];
+    const bool cacheable = ctx->params.cache_paths && range_steps * 20ull + (size_t)(o_end - o_begin) * m.nrays * 16ull <= ctx->params.path_cache_bytes;
+    const unsigned long long chunk_step_budget = cacheable ? ~0ull : std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / 20ull);
+    if (!(ctx->plan_cached && ctx->plan_o0 == o_begin && ctx->plan_o1 == o_end && cacheable)) {
+        ctx->drop_chunks();
+        uint32_t o = o_begin;
+        while (o < o_end) {
+            PathChunk* ch = new PathChunk();
+            ch->o0 = o;
+            unsigned long long s = 0;
+            while (o < o_end && (o - ch->o0) < max_o_scratch) {
+                const unsigned long long so = ctx->origin_steps[o - ctx->lens_o0];
+                if (o > ch->o0 && s + so > chunk_step_budget) break;
+                s += so; o++;
+            }
+            ch->o1 = o; ch->steps = s;
+            ctx->chunks.push_back(ch);
+        }
+        ctx->plan_o0 = o_begin; ctx->plan_o1 = o_end; ctx->plan_cached = cacheable;
+    }
+    // ---- outputs ----
+    // rows padded so that an in-place all-gather over nranks equal slices fits (mgb_allgather_results)
+    const size_t prow = (size_t)((m.npoints + ctx->nranks - 1) / ctx->nranks) * ctx->nranks;
+    MGB_CUDA(ctx, ctx->J.ensure(8 * prow * m.nfreqs));
+    MGB_CUDA(ctx, ctx->lam_val.ensure(8 * prow * m.nlines));
+    MGB_CUDA(ctx, ctx->lam_cnt.ensure(4 * prow * m.nlines));
+    double* u_full = nullptr;
+    if (ctx->params.store_intensities) {
+        MGB_CUDA(ctx, ctx->u_full.ensure(8 * (size_t)m.hnrays * (o_end - o_begin) * m.nfreqs));
+        u_full = ctx->u_full.as<double>(); ctx->u_o0 = o_begin; ctx->u_no = o_end - o_begin;
+    }
+    uint32_t max_no = 0;
+    for (auto* c : ctx->chunks) max_no = std::max(max_no, c->o1 - c->o0);
+    MGB_CUDA(ctx, ctx->scratch_u.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
+    MGB_CUDA(ctx, ctx->scratch_L.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
+    MGB_CUDA(ctx, ctx->counters.ensure(64));
+    MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+
+    bool all_cached = true;
+    for (auto* cp : ctx->chunks) {
+        PathChunk* ch = cp;
+        if (!cacheable) { /* reuse one workspace for every chunk */
+            ctx->work.o0 = cp->o0; ctx->work.o1 = cp->o1; ctx->work.steps = cp->steps; ctx->work.filled = false;
+            ch = &ctx->work;
+        }
+        if (!ch->filled) { all_cached = false; MGB_TRY(fill_chunk(ctx, *ch, &st, launches)); }
+        const uint32_t no = ch->o1 - ch->o0;
+        PathView pv{};
+        pv.o0 = ch->o0; pv.no = no; pv.len = ctx->lens.as<uint32_t>(); pv.poff = ch->poff.as<unsigned long long>();
+        pv.nr = ch->nr.as<uint32_t>(); pv.dZ = ch->dZ.as<double>(); pv.shift = ch->shift.as<double>(); pv.shift0 = ch->shift0.as<double>();
+        ScratchView sc{ctx->scratch_u.as<double>(), ctx->scratch_L.as<double>(), ctx->counters.as<unsigned long long>()};
+        EventTimer ts(ctx->stream);
+        ts.start();
+        if (approx == APPROX_NONE) launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f);
+        else if (approx == APPROX_ONELINE) launch_solve<APPROX_ONELINE>(ctx, pv, sc, nchunks_f);
+        else launch_solve<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f);
+        MGB_CUDA(ctx, cudaGetLastError());
+        st.ms_solve += ts.stop();
+        st.n_solve_launches++;
+        launches++;
+        EventTimer tr(ctx->stream);
+        tr.start();
+        const size_t nj = (size_t)no * m.nfreqs, nl = (size_t)no * m.nlines;
+        k_reduce_J<<<(unsigned)((nj + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J.as<double>(), u_full, ctx->u_o0, ctx->u_no);
+        k_reduce_lambda<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.L,
+                                                                               ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
+        MGB_CUDA(ctx, cudaGetLastError());
+        st.ms_reduce += tr.stop();
+        launches += 2;
+    }
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    st.ms_total = total.stop();
+    unsigned long long c[2];
+    MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 16, cudaMemcpyDeviceToHost));
+    st.n_entries = c[0]; st.n_large_shift = c[1];
+    st.n_steps = range_steps;
+    st.n_nbs_scanned = ctx->tot_scanned; /* of the counted range */
+    st.n_solves = (uint64_t)(o_end - o_begin) * m.hnrays * m.nfreqs;
+    st.max_ray_length = ctx->max_len;
+    st.n_chunks = (uint32_t)ctx->chunks.size();
+    st.n_launches = launches;
+    st.paths_cached = all_cached ? 1 : 0;
+    ctx->res_o0 = o_begin; ctx->res_o1 = o_end;
+    if (stats) *stats = st;
+    return MGB_OK;
+}
+
+static int check_range(mgb_ctx* ctx, uint32_t o0, uint32_t o1, const char* who) {
+    if (ctx->res_o1 <= ctx->res_o0) return ctx->fail(MGB_ESTATE, "%s: no results (run first)", who);
+    if (o0 >= o1 || o0 < ctx->res_o0 || o1 > ctx->res_o1)
+        if (!(ctx->nranks > 1 && o1 <= ctx->m.npoints && o0 < o1)) /* after an all-gather every row is valid */
+            return ctx->fail(MGB_EINVAL, "%s: range [%u,%u) outside the computed range [%u,%u)", who, o0, o1, ctx->res_o0, ctx->res_o1);
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_J(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J) {
+    if (!ctx || !J) return MGB_EINVAL;
+    MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_J"));
+    cudaSetDevice(ctx->device);
+    const size_t F = ctx->m.nfreqs;
+    MGB_CUDA(ctx, cudaMemcpy(J, ctx->J.as<double>() + (size_t)o_begin * F, 8 * (size_t)(o_end - o_begin) * F, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* lambda_val, uint32_t* lambda_cnt) {
+    if (!ctx || !lambda_val || !lambda_cnt) return MGB_EINVAL;
+    MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_lambda"));
+    cudaSetDevice(ctx->device);
+    const size_t L = ctx->m.nlines, n = (size_t)(o_end - o_begin) * L;
+    MGB_CUDA(ctx, cudaMemcpy(lambda_val, ctx->lam_val.as<double>() + (size_t)o_begin * L, 8 * n, cudaMemcpyDeviceToHost));
+    MGB_CUDA(ctx, cudaMemcpy(lambda_cnt, ctx->lam_cnt.as<uint32_t>() + (size_t)o_begin * L, 4 * n, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_u(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* u) {
+    if (!ctx || !u) return MGB_EINVAL;
+    if (!ctx->params.store_intensities || !ctx->u_full.p) return ctx->fail(MGB_ESTATE, "mgb_get_u: store_intensities was not set for the last run");
+    if (o_begin != ctx->u_o0 || o_end != ctx->u_o0 + ctx->u_no) return ctx->fail(MGB_EINVAL, "mgb_get_u: range must equal the run's range");
+    cudaSetDevice(ctx->device);
+    MGB_CUDA(ctx, cudaMemcpy(u, ctx->u_full.p, 8 * (size_t)ctx->m.hnrays * ctx->u_no * ctx->m.nfreqs, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const double* emissivity, const double* opacity,
+                                           const double* inverse_width, const double* population_tot, uint32_t o_begin,
+                                           uint32_t o_end, double* J, double* lambda_val, uint32_t* lambda_cnt, double* u,
+                                           mgb_stats* stats) {
+    if (!ctx) return MGB_EINVAL;
+    MGB_TRY(mgb_set_line_state(ctx, emissivity, opacity, inverse_width, population_tot));
+    MGB_TRY(mgb_run_feautrier_order_2(ctx, approx, o_begin, o_end, stats));
+    if (J) MGB_TRY(mgb_get_J(ctx, o_begin, o_end, J));
+    if (lambda_val && lambda_cnt) MGB_TRY(mgb_get_lambda(ctx, o_begin, o_end, lambda_val, lambda_cnt));
+    if (u) MGB_TRY(mgb_get_u(ctx, o_begin, o_end, u));
+    return MGB_OK;
+}
+
+extern "C" int mgb_result_ptrs_dev(mgb_ctx* ctx, void** J_dev, void** lambda_val_dev, void** lambda_cnt_dev) {
+    if (!ctx) return MGB_EINVAL;
+    if (!ctx->J.p) return ctx->fail(MGB_ESTATE, "mgb_result_ptrs_dev: no results yet");
+    if (J_dev) *J_dev = ctx->J.p;
+    if (lambda_val_dev) *lambda_val_dev = ctx->lam_val.p;
+    if (lambda_cnt_dev) *lambda_cnt_dev = ctx->lam_cnt.p;
+    return MGB_OK;
+}

@@ -1,0 +1,107 @@
+// mgb_ctx.h -- host-side context of libmagritte_b200.so (internal; the public surface is include/magritte_b200.h).
+#pragma once
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/magritte_b200.h"
+#include "mgb_device.cuh"
+
+namespace mgb {
+
+// Owning device allocation (grow-only reuse through ensure()).
+struct DevBuf {
+    void* p      = nullptr;
+    size_t bytes = 0;
+    ~DevBuf() { release(); }
+    DevBuf() = default;
+    DevBuf(const DevBuf&)            = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; bytes = 0;
+    }
+    cudaError_t ensure(size_t n) {
+        if (n <= bytes && p) return cudaSuccess;
+        release();
+        if (n == 0) n = 8;
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e == cudaSuccess) bytes = n; else p = nullptr;
+        return e;
+    }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct PathChunk {
+    uint32_t o0 = 0, o1 = 0;
+    unsigned long long steps = 0;
+    bool filled = false;
+    DevBuf poff, nr, dZ, shift, shift0;
+};
+
+} // namespace mgb
+
+struct mgb_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    mgb_params params;
+    bool have_geometry = false, have_thermo = false, have_lines = false, have_freqs = false, have_state = false;
+    bool points_dirty = true; // sqrtw_max / dshift_max need recomputing
+    // host copies of small tables
+    std::vector<uint32_t> nrad, nrad_cum, line_spec, line_k;
+    std::vector<double> inverse_mass;
+    double max_inverse_mass = 0.0;
+    mgb::DevModel m{};
+    // device storage
+    mgb::DevBuf pos, vel, csr, nbs, dir, weight, antipod, p2b, bcond, btemp;
+    mgb::DevBuf temperature, vturb2, sqrtw_max, dshift_max, inv_mass_dev;
+    mgb::DevBuf lrow, line, sorted_line, sorted_map, line_A, line_invmass, line_k_dev, line_spec_dev, line_quadw;
+    mgb::DevBuf nu, corr_line;
+    mgb::DevBuf stage_a, stage_b, stage_c, stage_d; // H2D staging of the per-iteration line state
+    // results
+    mgb::DevBuf J, lam_val, lam_cnt, u_full;
+    uint32_t u_o0 = 0, u_no = 0;
+    uint32_t res_o0 = 0, res_o1 = 0; // origin range of the last run
+    // tracing state
+    mgb::DevBuf lens;       // [npoints][nrays]
+    uint32_t lens_o0 = 0, lens_o1 = 0;
+    std::vector<unsigned long long> origin_steps; // per origin in [lens_o0, lens_o1)
+    unsigned long long tot_steps = 0, tot_scanned = 0;
+    uint32_t max_len = 0;
+    std::vector<mgb::PathChunk*> chunks; // cached path chunks (valid for plan_o0..plan_o1)
+    uint32_t plan_o0 = 0, plan_o1 = 0;
+    bool plan_cached = false;
+    mgb::PathChunk work;    // reusable chunk when paths are not cached
+    mgb::DevBuf scratch_u, scratch_L, counters, origin_tot, cub_tmp;
+    // NCCL
+    void* comm = nullptr;
+    int nranks = 1, rank = 0;
+
+    ~mgb_ctx();
+    int fail(int code, const char* fmt, ...) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        err = buf;
+        return code;
+    }
+    void drop_chunks() {
+        for (auto* c : chunks) delete c;
+        chunks.clear();
+        plan_cached = false;
+    }
+};
+
+#define MGB_CUDA(ctx, call)                                                                                         \
+    do {                                                                                                            \
+        cudaError_t e_ = (call);                                                                                    \
+        if (e_ != cudaSuccess) return (ctx)->fail(MGB_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                                  __FILE__, __LINE__);                                              \
+    } while (0)

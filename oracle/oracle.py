@@ -112,8 +112,11 @@ class Oracle:
         return dict(nr=nr[:k], nr_interp=nri[:k], interp_factor=fac[:k], shift=sh[:k], dZ=dz[:max(k - 1, 0)],
                     centre_offset=coff.value, n_tot=k)
 
-    def solve(self, o_range=None, rr_range=None, half_length=None):
+    def solve(self, o_range=None, rr_range=None, half_length=None, twosided=False):
+        """twosided=False: the reference's elimination order (the oracle). twosided=True: the product's two-sided
+        re-ordering of the same solve, restated operation for operation (bit-comparable with the CUDA kernel)."""
         m = self.m
+        self.lib.orc_set_twosided(C.c_int(1 if twosided else 0))
         o0, o1 = o_range or (0, m.npoints)
         r0, r1 = rr_range or (0, m.hnrays)
         hl = half_length or self.max_length()

@@ -1,0 +1,138 @@
+"""Parity of the CUDA path (through the C ABI of include/magritte_b200.h) with the reference.
+
+  * ray paths (nr, nr_interp, interp_factor, shift, dZ): bit-exact against the golden vectors dumped from the
+    compiled reference and against the oracle;
+  * J, Lambda, u: relative error <= 1e-10 (BASELINE.json north_star) against the reference's golden outputs, and
+    BIT-EXACT against the oracle's restatement of the product's two-sided elimination order.
+"""
+import numpy as np
+import pytest
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+TOL = 1e-10  # north_star: "J, level populations and images within a relative tolerance of 1e-10 in fp64"
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from magritte_b200 import cabi
+    c = cabi.Context(0)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_ray_paths_bit_exact(ctx, name):
+    flat, ref = util.load_golden(name)
+    ctx.set_model(flat)
+    for sel, want in util.golden_traces(ref):
+        util.assert_trace_equal(ctx.trace(*sel), want, f"{name} {sel}")
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+@pytest.mark.parametrize("cached", [False, True])
+def test_J_lambda_against_reference(ctx, name, cached):
+    from magritte_b200.flatten import approx_of
+    flat, ref = util.load_golden(name)
+    ctx.set_model(flat)
+    ctx.set_params(store_intensities=1)
+    approx = approx_of(flat["params"])
+    st = ctx.run(approx)
+    if cached:
+        st = ctx.run(approx)
+        assert st.paths_cached == 1
+    J = ctx.get_J()
+    assert util.relerr(J, ref["ref_J"]) <= TOL
+    val, cnt = ctx.get_lambda()
+    assert np.array_equal(cnt, ref["ref_lambda_cnt"])
+    assert util.relerr(val, ref["ref_lambda_val"]) <= TOL
+    if "ref_u" in ref:
+        assert util.relerr(ctx.get_u(), ref["ref_u"]) <= TOL
+    ctx.set_params(store_intensities=0)
+    assert st.n_solves == flat["npoints"] * flat["hnrays"] * flat["nfreqs"]
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+@pytest.mark.parametrize("approx", [0, 1, 2])
+def test_bit_exact_against_twosided_oracle(ctx, name, approx):
+    """All three ApproximationTypes; the oracle's two-sided variant performs the kernel's operations in the kernel's order."""
+    from oracle import oracle as orc
+    flat, ref = util.load_golden(name)
+    o = orc.Oracle(flat, approx=approx, store_u=False)
+    Jo = o.solve(twosided=True).copy()
+    ctx.set_model(flat)
+    st = ctx.run(approx)
+    J = ctx.get_J()
+    val, cnt = ctx.get_lambda()
+    assert st.n_steps == o.m.stat_steps and st.n_entries == o.m.stat_entries
+    assert np.array_equal(J, Jo), f"max rel err {util.relerr(J, Jo)}"
+    assert np.array_equal(cnt, o.L_cnt)
+    assert np.array_equal(val, o.L_val[:, :, 0])
+    # ... and the reference's own order stays within tolerance for every approximation
+    Jr = o.solve(twosided=False)
+    assert util.relerr(J, Jr) <= TOL
+
+
+def test_chunked_run_equals_single_chunk(ctx):
+    """Origin chunking (bounded scratch / path memory) must not change a single bit."""
+    flat, ref = util.load_golden("wind3d_small")
+    ctx.set_model(flat)
+    ctx.run(2)
+    J1 = ctx.get_J()
+    per_origin = flat["hnrays"] * flat["nfreqs"] * 16
+    ctx.set_params(scratch_bytes=per_origin * 100, path_cache_bytes=1 << 22, cache_paths=0)
+    st = ctx.run(2)
+    assert st.n_chunks > 5
+    assert np.array_equal(ctx.get_J(), J1)
+    ctx.set_params(scratch_bytes=0, path_cache_bytes=0, cache_paths=1)
+
+
+def test_origin_range_and_host_buffer_call(ctx):
+    flat, ref = util.load_golden("wind3d_small")
+    ctx.set_model(flat)
+    N = flat["npoints"]
+    J, (val, cnt), st = ctx.solve(flat["emissivity"], flat["opacity"], flat["inverse_width"], flat["population_tot"],
+                                  approx=2, o_range=(N // 3, 2 * N // 3))
+    assert util.relerr(J, ref["ref_J"][N // 3:2 * N // 3]) <= TOL
+    assert util.relerr(val, ref["ref_lambda_val"][N // 3:2 * N // 3]) <= TOL
+
+
+def test_errors_are_loud(ctx):
+    from magritte_b200 import cabi
+    c = cabi.Context(0)
+    with pytest.raises(cabi.MgbError):
+        c.npoints = 10
+        c.run(2)
+    with pytest.raises(cabi.MgbError):
+        c.set_params(n_off_diag=2)
+    c.close()
+
+
+@pytest.mark.parametrize("fn", ["expf", "logf", "erff", "expm1f", "powf"])
+def test_device_libm_bit_exact(ctx, fn):
+    """Device build of mgb_libm.h against the box's own libm on ~8 million inputs per function: a lattice over
+    all float bit patterns plus samples dense in the ranges the path feeds (profile exponents, h nu / kT, ratios)."""
+    import ctypes
+    import ctypes.util
+    libm = ctypes.CDLL(ctypes.util.find_library("m"))
+    rng = np.random.default_rng(3)
+    lattice = np.arange(0, 1 << 32, 1021, dtype=np.uint64).astype(np.uint32).view(np.float32)
+    dense = {"expf": -rng.uniform(0, 110, 1 << 22), "logf": np.exp(rng.uniform(-80, 80, 1 << 22)),
+             "erff": rng.uniform(-7, 7, 1 << 22), "expm1f": rng.uniform(0, 95, 1 << 22),
+             "powf": np.exp(rng.uniform(-60, 60, 1 << 22))}[fn].astype(np.float32)
+    x = np.concatenate([lattice, dense])
+    y = None
+    if fn == "powf":
+        n = rng.integers(2, 40, x.size)
+        y = (1.0 - (rng.integers(1, 40, x.size) % n) / n).astype(np.float32)
+    got = ctx.libm(fn, x, y)
+    f = getattr(libm, fn)
+    f.restype = ctypes.c_float
+    f.argtypes = [ctypes.c_float] * (2 if fn == "powf" else 1)
+    idx = rng.choice(x.size, 200000, replace=False)
+    want = np.array([f(float(x[i]), float(y[i])) if y is not None else f(float(x[i])) for i in idx], dtype=np.float32)
+    g = got[idx]
+    same = (g.view(np.uint32) == want.view(np.uint32)) | (np.isnan(g) & np.isnan(want))
+    assert same.all(), f"{fn}: {np.count_nonzero(~same)} mismatches, first x={x[idx][~same][:3]}"

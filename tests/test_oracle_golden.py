@@ -1,0 +1,36 @@
+"""The oracle (oracle/feautrier_oracle.c, a CPU restatement of the reference's path) against the golden
+vectors generated from the compiled, unmodified reference (tests/golden/make_golden.py): bit for bit."""
+import numpy as np
+import pytest
+
+import util
+from oracle import oracle as orc
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_oracle_bit_exact(name):
+    flat, ref = util.load_golden(name)
+    o = orc.Oracle(flat, store_u=True)
+    assert np.array_equal(o.dshift_max, ref["ref_dshift_max"])
+    assert 2 * o.max_length() + 1 == int(ref["ref_length"])  # Solver::setup: length = 2*max+1 (solver.tpp:4)
+    J = o.solve()
+    assert np.array_equal(J, ref["ref_J"]), f"max rel err {util.relerr(J, ref['ref_J'])}"
+    if "ref_u" in ref:
+        assert np.array_equal(o.u, ref["ref_u"])
+    assert np.array_equal(o.L_cnt, ref["ref_lambda_cnt"])
+    assert np.array_equal(o.L_val[:, :, 0], ref["ref_lambda_val"])
+    for sel, want in util.golden_traces(ref):
+        util.assert_trace_equal(o.trace(*sel), want, f"{name} {sel}")
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_twosided_reordering_error(name):
+    """The product eliminates the tridiagonal system from both ends (mgb_solve.cuh). Restated on the CPU, that
+    re-ordering must stay far inside the 1e-10 tolerance of BASELINE.json's north_star against the reference."""
+    flat, ref = util.load_golden(name)
+    o = orc.Oracle(flat, store_u=True)
+    J = o.solve(twosided=True).copy()
+    assert util.relerr(J, ref["ref_J"]) < 1e-12
+    assert util.relerr(o.L_val[:, :, 0], ref["ref_lambda_val"]) < 1e-12
+    if "ref_u" in ref:
+        assert util.relerr(o.u, ref["ref_u"]) < 1e-12

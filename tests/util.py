@@ -59,3 +59,45 @@ def lambda_dense(model, nlines):
                 out[(p, lid0 + k)] = sorted(zip(list(nr[p][k]), list(Ls[p][k])))
         lid0 += nrad
     return out
+
+
+GOLDEN_CASES = ["c1_all_constant", "c2_vanzadelhoff", "velgrad_1d", "wind3d_small", "wind3d_spiral_2spec"]
+
+
+def load_golden(name):
+    """-> (flat inputs dict as magritte_b200.flatten.flatten_model builds it, dict of reference outputs)."""
+    z = np.load(os.path.join(GOLDEN, f"case_{name}.npz"))
+    flat, ref, params = {}, {}, {}
+    for k in z.files:
+        v = z[k]
+        if k.startswith("param_"):
+            params[k[6:]] = v.item()
+        elif k.startswith("ref_") or k.startswith("trace_"):
+            ref[k] = v
+        else:
+            flat[k] = v.item() if v.ndim == 0 else np.ascontiguousarray(v)
+    flat["params"] = params
+    return flat, ref
+
+
+def golden_traces(ref):
+    """Yield ((o, rr, l), dict of arrays) for the ray paths stored in a golden file."""
+    pos = {k: 0 for k in ("nr", "nr_interp", "interp_factor", "shift", "dZ")}
+    for (o, rr, l), (n, coff) in zip(ref["trace_sel"], ref["trace_meta"]):
+        t = {}
+        for k in pos:
+            cnt = int(n) - 1 if k == "dZ" else int(n)
+            cnt = max(cnt, 0)
+            t[k] = ref["trace_" + k][pos[k]:pos[k] + cnt]
+            pos[k] += cnt
+        t["n_tot"], t["centre_offset"] = int(n), int(coff)
+        yield (int(o), int(rr), int(l)), t
+
+
+def assert_trace_equal(got, want, ctx=""):
+    assert got["n_tot"] == want["n_tot"], f"{ctx}: n_tot {got['n_tot']} != {want['n_tot']}"
+    assert got["centre_offset"] == want["centre_offset"], ctx
+    for k in ("nr", "nr_interp"):
+        assert np.array_equal(got[k], want[k]), f"{ctx}: {k} differs"
+    for k in ("interp_factor", "shift", "dZ"):
+        assert np.array_equal(np.asarray(got[k]).view(np.uint64), np.asarray(want[k]).view(np.uint64)), f"{ctx}: {k} not bit-identical"
