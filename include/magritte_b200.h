@@ -132,8 +132,12 @@ int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const double* emissivi
 /* Device addresses of the result buffers (full-size [npoints][nfreqs] / [npoints][nlines]) for in-place
  * collectives: replaces Radiation::MPI_reduce_J / Lambda::MPI_gather (radiation.cpp:76-91, lambda.tpp:121-206). */
 int mgb_result_ptrs_dev(mgb_ctx* ctx, void** J_dev, void** lambda_val_dev, void** lambda_cnt_dev);
-/* Drop cached ray paths (geometry unchanged): the next run traces again. */
+/* Drop the cached ray lengths and paths (geometry unchanged): the next run repeats the count pass and the trace. */
 int mgb_invalidate_paths(mgb_ctx* ctx);
+/* Device-side stopwatch on the context's stream (CUDA events): start, then stop returns elapsed milliseconds.
+ * For benchmarking a sequence of calls without host clocks. */
+int mgb_timer_start(mgb_ctx* ctx);
+int mgb_timer_stop(mgb_ctx* ctx, float* ms);
 
 /* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
 /* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */

@@ -17,7 +17,7 @@ EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
-    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition",
+    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition",
     "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak",
 ]
 
@@ -201,6 +201,14 @@ class Context:
 
     def invalidate_paths(self):
         self._check(self.lib.mgb_invalidate_paths(self._ctx), "mgb_invalidate_paths")
+
+    def timer_start(self):
+        self._check(self.lib.mgb_timer_start(self._ctx), "mgb_timer_start")
+
+    def timer_stop(self):
+        ms = C.c_float()
+        self._check(self.lib.mgb_timer_stop(self._ctx, C.byref(ms)), "mgb_timer_stop")
+        return ms.value
 
     # ---- multi-GPU --------------------------------------------------------------------------
     def nccl_unique_id(self):

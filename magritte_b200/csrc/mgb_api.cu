@@ -14,6 +14,8 @@ static std::string g_create_error;
 
 mgb_ctx::~mgb_ctx() {
     drop_chunks();
+    if (ev_a) cudaEventDestroy(ev_a);
+    if (ev_b) cudaEventDestroy(ev_b);
     if (stream) cudaStreamDestroy(stream);
 }
 
@@ -359,6 +361,26 @@ extern "C" int mgb_invalidate_paths(mgb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     for (auto* c : ctx->chunks) c->filled = false;
     ctx->work.filled = false;
+    ctx->lens_o0 = ctx->lens_o1 = 0;
+    ctx->drop_chunks();
+    return MGB_OK;
+}
+
+extern "C" int mgb_timer_start(mgb_ctx* ctx) {
+    if (!ctx) return MGB_EINVAL;
+    cudaSetDevice(ctx->device);
+    if (!ctx->ev_a) { MGB_CUDA(ctx, cudaEventCreate(&ctx->ev_a)); MGB_CUDA(ctx, cudaEventCreate(&ctx->ev_b)); }
+    MGB_CUDA(ctx, cudaEventRecord(ctx->ev_a, ctx->stream));
+    return MGB_OK;
+}
+
+extern "C" int mgb_timer_stop(mgb_ctx* ctx, float* ms) {
+    if (!ctx || !ms) return MGB_EINVAL;
+    if (!ctx->ev_a) return ctx->fail(MGB_ESTATE, "mgb_timer_stop without mgb_timer_start");
+    cudaSetDevice(ctx->device);
+    MGB_CUDA(ctx, cudaEventRecord(ctx->ev_b, ctx->stream));
+    MGB_CUDA(ctx, cudaEventSynchronize(ctx->ev_b));
+    MGB_CUDA(ctx, cudaEventElapsedTime(ms, ctx->ev_a, ctx->ev_b));
     return MGB_OK;
 }
 

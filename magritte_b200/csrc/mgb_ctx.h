@@ -48,6 +48,7 @@ struct PathChunk {
 struct mgb_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     std::string err;
     mgb_params params;
     bool have_geometry = false, have_thermo = false, have_lines = false, have_freqs = false, have_state = false;

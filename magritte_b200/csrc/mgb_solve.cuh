@@ -117,6 +117,8 @@ __global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchV
     if (len_b + len_f == 0) {
         // isolated origin (solver.tpp:510-518)
         if (active) { sc.u[out] = boundary_intensity(m, o, freq); sc.L[out] = 0.0; }
+        const unsigned e1 = __popc(__ballot_sync(0xffffffffu, active && z == 0)); /* n_tot = 1 per line */
+        if (lane == 0 && e1) atomicAdd(&sc.counters[0], (unsigned long long)e1);
         return;
     }
 
