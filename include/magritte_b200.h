@@ -159,6 +159,8 @@ int mgb_trace_dump(mgb_ctx* ctx, uint32_t o, uint32_t rr, uint32_t l, uint32_t c
 int mgb_selftest_libm(mgb_ctx* ctx, int fn, uint64_t n, const float* x, const float* y, float* out);
 /* Sustained DFMA rate of the device in TFLOP/s (2 flops per DFMA): the FP64 roofline denominator. */
 int mgb_measure_fp64_peak(mgb_ctx* ctx, double* tflops);
+/* Device division self-test: out[i] = the kernels' scaled IEEE division of a[i] / b[i] (must equal a[i] / b[i] bit for bit). */
+int mgb_selftest_ddiv(mgb_ctx* ctx, uint64_t n, const double* a, const double* b, double* out);
 
 #ifdef __cplusplus
 }

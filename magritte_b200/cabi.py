@@ -18,7 +18,7 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition",
-    "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak",
+    "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
 ]
 
 
@@ -252,6 +252,13 @@ class Context:
         code = {"expf": 0, "logf": 1, "erff": 2, "expm1f": 3, "powf": 4}[fn]
         self._check(self.lib.mgb_selftest_libm(self._ctx, C.c_int(code), C.c_uint64(x.size), px, py,
                                                out.ctypes.data_as(C.c_void_p)), "mgb_selftest_libm")
+        return out
+
+    def ddiv(self, a, b):
+        a, pa = _p(a, np.float64)
+        b, pb = _p(b, np.float64)
+        out = np.empty_like(a)
+        self._check(self.lib.mgb_selftest_ddiv(self._ctx, C.c_uint64(a.size), pa, pb, out.ctypes.data_as(C.c_void_p)), "mgb_selftest_ddiv")
         return out
 
     def fp64_peak_tflops(self):

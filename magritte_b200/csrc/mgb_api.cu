@@ -196,6 +196,9 @@ extern "C" int mgb_set_lines(mgb_ctx* ctx, uint32_t nlspecs, const uint32_t* nra
     MGB_TRY(upload(ctx, ctx->line_A, einstein_A, 8 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->sorted_line, sline.data(), 8 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->sorted_map, smap.data(), 4 * (size_t)nlines));
+    std::vector<uint32_t> spos(nlines);
+    for (uint32_t i = 0; i < nlines; i++) spos[smap[i]] = i;
+    MGB_TRY(upload(ctx, ctx->sorted_pos, spos.data(), 4 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->line_invmass, linv.data(), 8 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->line_k_dev, ctx->line_k.data(), 4 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->line_spec_dev, ctx->line_spec.data(), 4 * (size_t)nlines));
@@ -205,11 +208,34 @@ extern "C" int mgb_set_lines(mgb_ctx* ctx, uint32_t nlspecs, const uint32_t* nra
     DevModel& m = ctx->m;
     m.nlines = nlines; m.nlspecs = nlspecs; m.nquads = nquads;
     m.line = ctx->line.as<double>(); m.line_A = ctx->line_A.as<double>(); m.sorted_line = ctx->sorted_line.as<double>();
-    m.sorted_map = ctx->sorted_map.as<uint32_t>(); m.line_invmass = ctx->line_invmass.as<double>();
+    m.sorted_map = ctx->sorted_map.as<uint32_t>(); m.sorted_pos = ctx->sorted_pos.as<uint32_t>(); m.line_invmass = ctx->line_invmass.as<double>();
     m.line_k = ctx->line_k_dev.as<uint32_t>(); m.line_quadw = ctx->line_quadw.as<double>();
     ctx->have_lines = true;
     ctx->have_state = ctx->have_freqs = false;
     ctx->points_dirty = true;
+    return MGB_OK;
+}
+
+// k_solve's work decomposition: consecutive frequency bins, <= 32 per warp, spanning <= lines_per_warp lines.
+static int build_freq_chunks(mgb_ctx* ctx) {
+    const uint32_t nq = ctx->m.nquads, nf = ctx->m.nfreqs;
+    uint32_t lpw = nq >= 32 ? 2 : (31 + nq - 1) / nq + 1;
+    if (lpw > 8) lpw = 8;
+    if (lpw > ctx->m.nlines) lpw = ctx->m.nlines;
+    std::vector<FreqChunk> ch;
+    for (uint32_t f0 = 0; f0 < nf;) {
+        const uint32_t l0 = f0 / nq;
+        uint32_t f1 = std::min(nf, f0 + 32);
+        f1 = std::min(f1, (l0 + lpw) * nq);
+        FreqChunk c;
+        c.f0 = f0; c.nf = f1 - f0; c.l0 = l0; c.nl = (f1 - 1) / nq - l0 + 1;
+        ch.push_back(c);
+        f0 = f1;
+    }
+    MGB_TRY(upload(ctx, ctx->freq_chunks, ch.data(), sizeof(FreqChunk) * ch.size()));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->n_freq_chunks = (uint32_t)ch.size();
+    ctx->lines_per_warp = lpw;
     return MGB_OK;
 }
 
@@ -225,6 +251,7 @@ extern "C" int mgb_set_frequencies(mgb_ctx* ctx, uint32_t nfreqs, const double* 
     MGB_TRY(upload(ctx, ctx->corr_line, corresponding_line, 4 * (size_t)nfreqs));
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->m.nfreqs = nfreqs; ctx->m.nu = ctx->nu.as<double>(); ctx->m.corr_line = ctx->corr_line.as<uint32_t>();
+    MGB_TRY(build_freq_chunks(ctx));
     ctx->have_freqs = true;
     return MGB_OK;
 }
@@ -348,10 +375,15 @@ int fill_chunk(mgb_ctx* ctx, PathChunk& ch, mgb_stats* st, uint32_t& launches) {
 }
 
 template <int APPROX>
-void launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
+cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
     const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
     const size_t blocks = (nitems * 32 + 127) / 128;
-    k_solve<APPROX><<<(unsigned)blocks, 128, 0, ctx->stream>>>(ctx->m, pv, sc, nchunks_f);
+    const size_t smem   = 4 * solve_smem_per_warp(ctx->lines_per_warp);
+    cudaError_t e = cudaFuncSetAttribute(k_solve<APPROX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_solve<APPROX><<<(unsigned)blocks, 128, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
+                                                                  ctx->lines_per_warp);
+    return cudaGetLastError();
 }
 
 } // namespace
@@ -402,7 +434,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     MGB_TRY(refresh_points(ctx));
     MGB_TRY(ensure_lens(ctx, o_begin, o_end, &st, launches));
 
-    const uint32_t nchunks_f = (m.nfreqs + 31) / 32;
+    const uint32_t nchunks_f = ctx->n_freq_chunks;
     // ---- plan origin chunks: bounded scratch (16 B per solve) and bounded path bytes (20 B per step) ----
     const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * 16;
     const uint32_t max_o_scratch    = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / per_origin_scratch);
@@ -460,10 +492,9 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         ScratchView sc{ctx->scratch_u.as<double>(), ctx->scratch_L.as<double>(), ctx->counters.as<unsigned long long>()};
         EventTimer ts(ctx->stream);
         ts.start();
-        if (approx == APPROX_NONE) launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f);
-        else if (approx == APPROX_ONELINE) launch_solve<APPROX_ONELINE>(ctx, pv, sc, nchunks_f);
-        else launch_solve<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f);
-        MGB_CUDA(ctx, cudaGetLastError());
+        if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f));
+        else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_solve<APPROX_ONELINE>(ctx, pv, sc, nchunks_f));
+        else MGB_CUDA(ctx, launch_solve<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f));
         st.ms_solve += ts.stop();
         st.n_solve_launches++;
         launches++;

@@ -57,11 +57,12 @@ struct mgb_ctx {
     std::vector<uint32_t> nrad, nrad_cum, line_spec, line_k;
     std::vector<double> inverse_mass;
     double max_inverse_mass = 0.0;
+    uint32_t n_freq_chunks = 0, lines_per_warp = 1; // k_solve work decomposition (build_freq_chunks)
     mgb::DevModel m{};
     // device storage
     mgb::DevBuf pos, vel, csr, nbs, dir, weight, antipod, p2b, bcond, btemp;
     mgb::DevBuf temperature, vturb2, sqrtw_max, dshift_max, inv_mass_dev;
-    mgb::DevBuf lrow, line, sorted_line, sorted_map, line_A, line_invmass, line_k_dev, line_spec_dev, line_quadw;
+    mgb::DevBuf lrow, line, sorted_line, sorted_map, sorted_pos, freq_chunks, line_A, line_invmass, line_k_dev, line_spec_dev, line_quadw;
     mgb::DevBuf nu, corr_line;
     mgb::DevBuf stage_a, stage_b, stage_c, stage_d; // H2D staging of the per-iteration line state
     // results

@@ -75,6 +75,11 @@ __global__ void k_libm(int fn, unsigned long long n, const float* x, const float
     out[i] = r;
 }
 
+__global__ void k_ddiv(unsigned long long n, const double* a, const double* b, double* out) {
+    const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = ddiv(a[i], b[i]);
+}
+
 // 8 independent DFMA chains per thread; explicit fma() because the file is compiled with -fmad=false.
 __global__ void k_dfma(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -177,5 +182,19 @@ extern "C" int mgb_measure_fp64_peak(mgb_ctx* ctx, double* tflops) {
     cudaEventDestroy(a); cudaEventDestroy(b);
     MGB_CUDA(ctx, cudaGetLastError());
     *tflops = best;
+    return MGB_OK;
+}
+
+extern "C" int mgb_selftest_ddiv(mgb_ctx* ctx, uint64_t n, const double* a, const double* b, double* out) {
+    if (!ctx || !a || !b || !out) return MGB_EINVAL;
+    cudaSetDevice(ctx->device);
+    DevBuf da, db, dout;
+    MGB_CUDA(ctx, da.ensure(8 * n)); MGB_CUDA(ctx, db.ensure(8 * n)); MGB_CUDA(ctx, dout.ensure(8 * n));
+    MGB_CUDA(ctx, cudaMemcpy(da.p, a, 8 * n, cudaMemcpyHostToDevice));
+    MGB_CUDA(ctx, cudaMemcpy(db.p, b, 8 * n, cudaMemcpyHostToDevice));
+    k_ddiv<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(n, da.as<double>(), db.as<double>(), dout.as<double>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    MGB_CUDA(ctx, cudaMemcpy(out, dout.p, 8 * n, cudaMemcpyDeviceToHost));
     return MGB_OK;
 }

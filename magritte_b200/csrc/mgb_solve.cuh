@@ -1,26 +1,203 @@
-// mgb_solve.cuh -- k_solve: eta/chi assembly + second-order Feautrier solve, lanes = frequency bins.
+// mgb_solve.cuh -- k_solve: eta/chi assembly + second-order Feautrier solve.
 //
-// One warp owns (origin o, ray pair rr, 32 consecutive frequency bins). Every lane walks the cached
-// geometric path of both half-rays from the far (boundary) end towards the origin, expands each step
-// into the reference's sub-steps for ITS line (Solver::set_data_for_line, solver.tpp:1057-1097),
-// evaluates eta, chi, S and dtau exactly as compute_source_dtau does (solver.tpp:2139-2186) and
-// eliminates the tridiagonal system from both ends simultaneously:
+// Work item = one warp = (origin o, ray pair rr, one chunk of <= 32 consecutive frequency bins, which belong
+// to <= LPW lines). The warp alternates between two phases over the cached geometric path of each half-ray,
+// walking from the far (boundary) end towards the origin:
 //
+//   phase A  (lanes = ray ENTRIES of one line): expands the next 32 entries of that line's ray -- the reference's
+//            sub-stepping Solver::set_data_for_line (solver.tpp:1057-1097) with n_interp from
+//            InterpHelper::get_n_interp_for_line (solver_interp_helper.tpp:55-75) -- and evaluates everything that
+//            does not depend on the frequency bin ONCE per (entry, line): Doppler shift, segment length, the
+//            interpolated inverse width / emissivity / opacity of the line (interp_linear / interp_log with powf,
+//            solver.tpp:1259-1302), the line source function of the line-integrated branch (:1888-1911) and the
+//            per-point dshift_max / CloseLines window width. Records go to shared memory (SoA, 32 per line).
+//   phase B  (lanes = FREQUENCY bins): every lane streams over its line's 32 records and does the per-frequency
+//            work: CloseLines window test, Gaussian profile (bit-exact expf), eta, chi, S, dtau
+//            (compute_source_dtau, solver.tpp:2139-2186, incl. the erff line-integrated branch) and one step of
+//            the elimination, all in registers.
+//
+// The tridiagonal system is eliminated from both ends simultaneously:
 //   first side  (entries first..centre-1):  the reference's own forward elimination (FF, Su; :2240-2297)
-//   last side   (entries last..centre+1):   its mirror image (GG, and the mirrored Su), which the reference
+//   last side   (entries last..centre+1):   its mirror image (GG and the mirrored Su), which the reference
 //                                           already uses for L_diag (:2302-2315)
 //   centre row:  u_c = (S_c + A_c a_{c-1} + C_c a'_{c+1}) * L_diag,  L_diag = inverse_C/(FF_c + GP_{c+1})
+// so no per-entry coefficient array is ever stored. This is algebraically the reference's forward-elimination/
+// back-substitution (solver.tpp:2193-2356, n_off_diag = 0); only the rounding of the elimination differs
+// (observed |dJ/J| < 1e-13, tests/test_oracle_golden.py::test_twosided_reordering_error).
 //
-// so no per-entry coefficient array is ever stored: the whole solve lives in registers. This is
-// algebraically the reference's forward-elimination/back-substitution (solver.tpp:2193-2356, n_off_diag = 0);
-// only the rounding of the elimination differs (observed |dJ/J| < 1e-13, tests/test_twosided_error.py).
+// The common case -- the CloseLines window of a bin contains exactly the bin's own line -- is served from the
+// phase-A record with four comparisons against the neighbouring sorted line centres (exactly the result of
+// the reference's std::lower_bound/upper_bound, solver.tpp:1230-1233); anything else (overlapping lines,
+// ApproximationType None, a OneLine bin whose corresponding_line is another line) takes the generic
+// out-of-line path that loads and interpolates every line in the window like the reference does.
 #pragma once
 #include "mgb_kernels.cuh"
 
 namespace mgb {
 
+// chunk of consecutive frequency bins handled by one warp (built on the host, mgb_api.cu: build_freq_chunks)
+struct FreqChunk {
+    uint32_t f0, nf; // bins [f0, f0+nf), nf <= 32
+    uint32_t l0, nl; // lines l0 .. l0+nl-1 own those bins (f = l*nquads + z), nl <= lpw
+};
+
+constexpr int kRecStride = 34;       // doubles per (field, line) row: 32 entries + 2 pad (distinct banks per line)
+constexpr int kRecFields = 9;        // shift, dz, iw, ie, io, sline, dsm, sqw, factor
+enum { R_SHIFT = 0, R_DZ, R_IW, R_IE, R_IO, R_SLINE, R_DSM, R_SQW, R_FACTOR };
+
+constexpr int kWordsPerLine = 102;   // u32 per line: ni[32], excl[32], eoff[36], isub, pad
+constexpr int kLineDoubles  = kRecFields * kRecStride + 32 /* p1,p2 */ + kWordsPerLine / 2;
+
+// bytes of dynamic shared memory per warp
+__host__ __device__ inline size_t solve_smem_per_warp(uint32_t lpw) { return 8 * ((size_t)lpw * kLineDoubles + 6 * 32 /* side-0 results */); }
+
+// Per-warp shared-memory region, addressed with 32-bit indices into the block's dynamic shared array so that
+// every record access is one LDS/STS with an immediate offset.
+extern __shared__ __align__(16) double mgb_smem[];
+struct WarpSmem {
+    uint32_t base; // index (in doubles) of this warp's region
+    uint32_t lpw;
+    __device__ __forceinline__ double* field(uint32_t k, int fld) const { return mgb_smem + base + (k * kRecFields + fld) * kRecStride; } // [32]
+    __device__ __forceinline__ uint2* pts() const { return reinterpret_cast<uint2*>(mgb_smem + base + lpw * kRecFields * kRecStride); }  // [lpw][32]
+    __device__ __forceinline__ uint32_t* words(uint32_t k) const {
+        return reinterpret_cast<uint32_t*>(mgb_smem + base + lpw * (kRecFields * kRecStride + 32)) + k * kWordsPerLine;
+    }
+    __device__ __forceinline__ uint32_t* ni(uint32_t k) const { return words(k); }         // [32] sub-steps of step j-1-lane
+    __device__ __forceinline__ uint32_t* excl(uint32_t k) const { return words(k) + 32; }  // [32] exclusive prefix of ni
+    __device__ __forceinline__ uint32_t* eoff(uint32_t k) const { return words(k) + 64; }  // [S+1] entry offset of each step in the buffer
+    __device__ __forceinline__ uint32_t* isub(uint32_t k) const { return words(k) + 100; } // sub-entries of step j-1 already emitted
+    __device__ __forceinline__ double* side0(unsigned lane) const { return mgb_smem + base + lpw * kLineDoubles + lane; } // [6][32]
+};
+
+// A ray entry as phase B sees it (registers).
+struct Rec {
+    double shift, iw, io, sline, dsm, sqw, factor;
+    uint32_t p1, p2;
+};
+
+// ---------------------------------------------------------------------------------------------------
+// generic (out-of-line) paths: exactly the reference's loops over the lines in the window
+// ---------------------------------------------------------------------------------------------------
+template <int APPROX>
+__device__ __noinline__ void eta_chi_generic(const DevModel& m, uint32_t p1, uint32_t p2, double factor, uint32_t ll, double freq,
+                                             double& eta, double& chi) {
+    Entry e;
+    e.p1 = p1; e.p2 = p2; e.factor = factor; e.shift = 1.0;
+    eta_chi_interp<APPROX>(m, e, ll, freq, eta, chi);
+}
+
+template <int APPROX>
+__device__ __noinline__ void S_dtau_generic(const DevModel& m, uint32_t cp1, uint32_t cp2, double cfac, uint32_t np1, uint32_t np2,
+                                            double nfac, uint32_t ll, double currfreq, double nextfreq, double dz, double& dtau,
+                                            double& Scurr, double& Snext) {
+    Entry c, n;
+    c.p1 = cp1; c.p2 = cp2; c.factor = cfac; c.shift = 1.0;
+    n.p1 = np1; n.p2 = np2; n.factor = nfac; n.shift = 1.0;
+    S_dtau_line_integrated<APPROX>(m, c, n, ll, currfreq, nextfreq, dz, dtau, Scurr, Snext);
+}
+
+// per-lane constants of the bin's own line
+struct LaneLine {
+    double s_prev, s_own, s_next; // sorted line centres around the own line (-inf / +inf sentinels)
+    bool own;                     // the record of line l may be used for this bin's eta/chi
+};
+
+// Classify the CloseLines window [left,right] against the sorted line list using only the own line's neighbours.
+// With lo = lower_bound(left), hi = upper_bound(right) (solver.tpp:1230-1233) and pos = sorted position of the own line:
+//   WIN_OWN   : lo == pos && hi == pos+1   (exactly the own line)
+//   WIN_EMPTY : lo >= hi                   (no line: the bin is Doppler-shifted out of every line's reach)
+//   WIN_OTHER : anything else (or NaN)  -> generic path
+enum { WIN_OTHER = 0, WIN_OWN = 1, WIN_EMPTY = 2 };
+__device__ __forceinline__ int window_class(const LaneLine& L, double left, double right) {
+    if (!L.own) return WIN_OTHER;
+    const bool prev_below = L.s_prev < left, own_below = L.s_own < left;
+    const bool own_above = right < L.s_own, next_above = right < L.s_next;
+    if (prev_below && !own_below && !own_above && next_above) return WIN_OWN;
+    if ((prev_below && own_above) || (own_below && next_above)) return WIN_EMPTY;
+    return WIN_OTHER;
+}
+
+// get_eta_and_chi_interpolated at one entry, then S = eta/chi (solver.tpp:2166-2176)
+template <int APPROX>
+__device__ __forceinline__ void eval_rec(const DevModel& m, const LaneLine& L, const Rec& r, double ie, uint32_t ll, double freq,
+                                         double& chi, double& S) {
+    const double fr = freq * r.shift;
+    double eta;
+    int cls = WIN_OTHER;
+    if (APPROX == APPROX_CLOSELINES) {
+        const double ub = m.max_dist * (fr * r.sqw);
+        cls = window_class(L, fr - ub, fr + ub);
+    } else if (APPROX == APPROX_ONELINE) {
+        cls = L.own ? WIN_OWN : WIN_OTHER;
+    }
+    if (cls == WIN_OWN) {
+        const double prof = gaussian(r.iw, fr - L.s_own);
+        /* the reference accumulates into eta = 0, chi = min_opacity (CloseLines) or adds min_opacity last (OneLine) */
+        eta = 0.0 + prof * ie;
+        if (APPROX == APPROX_ONELINE) chi = (0.0 + prof * r.io) + m.min_opacity;
+        else chi = m.min_opacity + prof * r.io;
+    } else if (cls == WIN_EMPTY) {
+        eta = 0.0; chi = m.min_opacity;
+    } else {
+        eta_chi_generic<APPROX>(m, r.p1, r.p2, r.factor, ll, fr, eta, chi);
+    }
+    S = ddiv(eta, chi);
+}
+
+// compute_S_dtau_line_integrated for the segment c -> n (reference orientation), from the records when the
+// window holds exactly the own line (solver.tpp:1878-1912 OneLine, 2012-2111 CloseLines; compute_dtau_single_line :2374-2455)
+template <int APPROX>
+__device__ __forceinline__ void S_dtau_rec(const DevModel& m, const LaneLine& L, const Rec& c, const Rec& n, uint32_t ll, double currfreq,
+                                           double nextfreq, double dz, double& dtau, double& Scurr, double& Snext) {
+    int cls = WIN_OTHER;
+    if (APPROX == APPROX_CLOSELINES) {
+        double left_freq, right_freq;
+        if (currfreq < nextfreq) { left_freq = currfreq; right_freq = nextfreq; }
+        else { right_freq = currfreq; left_freq = nextfreq; }
+        const double cb = m.max_dist * (right_freq * c.sqw);
+        const double nb = m.max_dist * (right_freq * n.sqw);
+        const double ub = (cb < nb) ? nb : cb;
+        cls = window_class(L, left_freq - ub, right_freq + ub);
+    } else if (APPROX == APPROX_ONELINE) {
+        cls = L.own ? WIN_OWN : WIN_OTHER;
+    }
+    if (cls == WIN_OTHER) {
+        S_dtau_generic<APPROX>(m, c.p1, c.p2, c.factor, n.p1, n.p2, n.factor, ll, currfreq, nextfreq, dz, dtau, Scurr, Snext);
+        return;
+    }
+    if (cls == WIN_EMPTY) { /* no line in reach: sums stay 0, dtau is bounded below by min_opacity*dz (solver.tpp:2095-2110) */
+        double d = 0.0;
+        const double bound_min_dtau = m.min_opacity * dz;
+        if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
+        dtau = d; Scurr = 0.0 / d; Snext = 0.0 / d;
+        return;
+    }
+    const double linefreq = L.s_own;
+    const double avg_iw   = (c.iw + n.iw) / 2.0;
+    double ld;
+    if (currfreq == nextfreq) {
+        const double prof   = gaussian(avg_iw, currfreq - linefreq);
+        const double avg_op = (c.io + n.io) / 2.0;
+        ld = dz * (prof * avg_op + m.min_opacity);
+    } else {
+        const double next_pos = (linefreq - nextfreq) * avg_iw;
+        const double curr_pos = (linefreq - currfreq) * avg_iw;
+        const double diff_pos = next_pos - curr_pos;
+        const double avg_op   = (n.io + c.io) / 2.0;
+        const float erfdiff   = erff_ool((float)next_pos) - erff_ool((float)curr_pos); /* float subtraction */
+        const double erfterm  = ddiv(avg_op, diff_pos) / 2.0 * (double)erfdiff;
+        ld = dz * (avg_iw * erfterm + m.min_opacity);
+    }
+    if (APPROX == APPROX_ONELINE) { dtau = ld; Scurr = c.sline; Snext = n.sline; return; }
+    const double sum_dtau = 0.0 + ld, sum_c = 0.0 + ld * c.sline, sum_n = 0.0 + ld * n.sline;
+    double d = sum_dtau;
+    const double bound_min_dtau = m.min_opacity * dz;
+    if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
+    dtau = d; Scurr = ddiv(sum_c, d); Snext = ddiv(sum_n, d);
+}
+
 struct SideState {
-    Entry X;          // the far entry of the segment being closed
+    Rec X;            // the far entry of the segment being closed
     double chiX, SX;  // eta/chi evaluation at X
     double dzX;       // length of the segment between X and its nearer neighbour
     double dtau_far;  // optical depth of X's far segment
@@ -29,29 +206,22 @@ struct SideState {
     bool haveX, X_is_end, large_far;
 };
 
-template <int APPROX>
-__device__ __forceinline__ void eval_entry(const DevModel& m, const Entry& e, uint32_t ll, double freq, double& chi, double& S) {
-    double eta;
-    eta_chi_interp<APPROX>(m, e, ll, freq * e.shift, eta, chi);
-    S = eta / chi;
-}
-
 // Close the segment between the far entry st.X and the nearer entry Y, then advance.
 // side 0: reference orientation curr = X, next = Y.  side 1: curr = Y, next = X.
 template <int APPROX>
-__device__ __forceinline__ void push_entry(const DevModel& m, SideState& st, int side, const Entry& Y, double chiY, double SY, double dzY,
-                                           uint32_t ll, double freq, unsigned& nlarge) {
+__device__ __forceinline__ void push_rec(const DevModel& m, const LaneLine& L, SideState& st, int side, const Rec& Y, double chiY,
+                                         double SY, double dzY, uint32_t ll, double freq, unsigned& nlarge) {
     if (st.haveX) {
-        const Entry& c = side ? Y : st.X;
-        const Entry& n = side ? st.X : Y;
+        const Rec& c = side ? Y : st.X;
+        const Rec& n = side ? st.X : Y;
         // compute_source_dtau (solver.tpp:2139-2186)
         const double dshift_abs = fabs(n.shift - c.shift);
-        const double da = __ldg(&m.dshift_max[c.p1]), db = __ldg(&m.dshift_max[n.p1]);
+        const double da = c.dsm, db = n.dsm;
         const double dshift_max = (db < da) ? db : da;
         double dtau, Scurr = 0.0, Snext = 0.0;
         const bool large = dshift_abs > dshift_max;
         if (large) {
-            S_dtau_line_integrated<APPROX>(m, c, n, ll, freq * c.shift, freq * n.shift, st.dzX, dtau, Scurr, Snext);
+            S_dtau_rec<APPROX>(m, L, c, n, ll, freq * c.shift, freq * n.shift, st.dzX, dtau, Scurr, Snext);
             nlarge++;
         } else {
             const double chic = side ? chiY : st.chiX, chin = side ? st.chiX : chiY;
@@ -60,23 +230,23 @@ __device__ __forceinline__ void push_entry(const DevModel& m, SideState& st, int
         if (st.X_is_end) {
             // boundary row (solver.tpp:2240-2262 for `first`, 2283-2297 mirrored for `last`)
             const double S0 = large ? (side ? Snext : Scurr) : st.SX;
-            const double inv = 1.0 / dtau;
+            const double inv = ddiv(1.0, dtau);
             const double Cb  = 2.0 * inv * inv;
             const double Bm  = 1.0 + 2.0 * inv;
             const double B   = Bm + Cb;
             const double Ib  = boundary_intensity(m, st.X.p1, freq * st.X.shift);
-            st.a  = (S0 + 2.0 * Ib * inv) / B;
+            st.a  = ddiv(S0 + 2.0 * Ib * inv, B);
             st.F  = 0.5 * Bm * dtau * dtau;
-            st.FI = 1.0 / (1.0 + st.F);
+            st.FI = ddiv(1.0, 1.0 + st.F);
         } else {
             // interior row (solver.tpp:2264-2281; mirrored 2306-2311)
             const double Sx = side ? (st.large_far ? st.Scurr_far : st.SX) : (large ? Scurr : st.SX);
             const double avg     = 0.5 * (st.dtau_far + dtau);
             const double invFar  = avg * st.dtau_far;
             const double invNear = avg * dtau;
-            const double Afar    = 1.0 / invFar;
+            const double Afar    = ddiv(1.0, invFar);
             st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-            st.FI = 1.0 / (1.0 + st.F);
+            st.FI = ddiv(1.0, 1.0 + st.F);
             st.a  = (Afar * st.a + Sx) * st.FI * invNear;
         }
         st.dtau_far  = dtau;
@@ -91,26 +261,181 @@ __device__ __forceinline__ void push_entry(const DevModel& m, SideState& st, int
     st.X = Y; st.chiX = chiY; st.SX = SY; st.dzX = dzY;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// phase A: one record = everything of a ray entry that does not depend on the frequency bin
+// (Solver::set_data_for_line, solver.tpp:1057-1097, fused with the interpolation part of
+// get_eta_and_chi_interpolated, :1259-1302, and the line source function of :1888-1911)
+// ---------------------------------------------------------------------------------------------------
+struct StepData { // one geometric step crt -> nxt of the cached path (independent of the line)
+    uint32_t nxt, crt;
+    double dZ, sh_nxt, sh_crt, dsm, sqw;
+};
+
+__device__ __forceinline__ void make_record(const DevModel& m, const WarpSmem& ws, uint32_t k, uint32_t l, uint32_t slot, const StepData& sd,
+                                            uint32_t i, uint32_t ni) {
+    double dz = sd.dZ, factor = 0.0, shift = sd.sh_nxt;
+    if (ni > 1) {
+        dz = sd.dZ / ni;
+        const double dshi = (sd.sh_nxt - sd.sh_crt) / ni;
+        factor = 1.0 - ((double)i) / ni;
+        shift  = sd.sh_crt + i * dshi;
+    }
+    const LineRow a = load_row(m, sd.nxt, l);
+    double iw = a.inverse_width, ie = a.emissivity, io = a.opacity;
+    double sline = ddiv(a.emissivity, a.opacity);
+    if (factor != 0.0) {
+        const LineRow b = load_row(m, sd.crt, l);
+        iw    = interp_linear(a.inverse_width, b.inverse_width, factor);
+        ie    = interp_log(a.emissivity, b.emissivity, factor);
+        io    = interp_log(a.opacity, b.opacity, factor);
+        sline = interp_log(sline, ddiv(b.emissivity, b.opacity), factor);
+    }
+    double* r = ws.field(k, 0) + slot;
+    r[R_SHIFT * kRecStride]  = shift;
+    r[R_DZ * kRecStride]     = dz;
+    r[R_IW * kRecStride]     = iw;
+    r[R_IE * kRecStride]     = ie;
+    r[R_IO * kRecStride]     = io;
+    r[R_SLINE * kRecStride]  = sline;
+    r[R_DSM * kRecStride]    = sd.dsm;
+    r[R_SQW * kRecStride]    = sd.sqw;
+    r[R_FACTOR * kRecStride] = factor;
+    ws.pts()[k * 32 + slot]  = make_uint2(sd.nxt, sd.crt);
+}
+
+// Expand the next geometric steps j-1, j-2, ... of the half-ray for all nl lines of the warp. Returns the number S of
+// steps whose entries are now in the record buffers (eoff(k)[0..S] = entry offsets per step of line k); all lines
+// advance by the SAME steps so that phase B runs in lock-step over segments (uniform large/small-shift branch).
+// S is limited by the 32 record slots per line. A single step with more than 32 sub-steps on some line is
+// emitted 32 entries at a time (isub cursors) and reported as S = 1 with j unchanged until every line is through.
+__device__ __forceinline__ uint32_t produce_window(const DevModel& m, const PathView& pv, const WarpSmem& ws, uint32_t l0, uint32_t nl,
+                                                   uint32_t o, unsigned long long off, double shift0, uint32_t& j, unsigned lane) {
+    // ---- lanes = steps ----
+    const int js = (int)j - 1 - (int)lane;
+    StepData sd;
+    sd.nxt = o; sd.crt = o; sd.dZ = 0.0; sd.sh_nxt = 1.0; sd.sh_crt = 1.0; sd.dsm = 0.0; sd.sqw = 0.0;
+    if (js >= 0) {
+        sd.nxt    = __ldg(&pv.nr[off + js]);
+        sd.crt    = js ? __ldg(&pv.nr[off + js - 1]) : o;
+        sd.dZ     = __ldg(&pv.dZ[off + js]);
+        sd.sh_nxt = __ldg(&pv.shift[off + js]);
+        sd.sh_crt = js ? __ldg(&pv.shift[off + js - 1]) : shift0;
+        sd.dsm    = __ldg(&m.dshift_max[sd.nxt]);
+        sd.sqw    = __ldg(&m.sqrtw_max[sd.nxt]);
+    }
+    uint32_t S = j < 32u ? j : 32u;
+    for (uint32_t k = 0; k < nl; k++) {
+        uint32_t ni = 0;
+        if (js >= 0) {
+            const double crit_nxt = __ldg(&m.lrow[(size_t)sd.nxt * m.nlines + l0 + k].criterion);
+            const double crit_crt = __ldg(&m.lrow[(size_t)sd.crt * m.nlines + l0 + k].criterion);
+            ni = n_interp_from_criteria(m, crit_crt, crit_nxt);
+        }
+        uint32_t cum = ni;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, cum, d);
+            if ((int)lane >= d) cum += v;
+        }
+        ws.ni(k)[lane]   = ni;
+        ws.excl(k)[lane] = cum - ni;
+        const uint32_t fits = __ballot_sync(0xffffffffu, cum <= 32u);
+        const uint32_t Sk   = (fits == 0xffffffffu) ? 32u : (uint32_t)(__ffs(~fits) - 1);
+        S = Sk < S ? Sk : S;
+    }
+    __syncwarp();
+    if (S > 0) {
+        for (uint32_t k = 0; k < nl; k++) {
+            const uint32_t ni = (lane < S) ? ws.ni(k)[lane] : 0u, excl = ws.excl(k)[lane];
+            const uint32_t total = __shfl_sync(0xffffffffu, excl + ni, S - 1); /* <= 32 entries in this window */
+            // ---- entry e -> the step that owns it: scatter step ids at their first entry, then a running maximum ----
+            uint32_t* mark = ws.eoff(k); /* eoff doubles as the scatter array before it receives the offsets */
+            mark[lane] = 0;
+            __syncwarp();
+            if (lane < S) mark[excl] = lane + 1;
+            __syncwarp();
+            uint32_t te1 = mark[lane];
+            __syncwarp();
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, te1, d);
+                if ((int)lane >= d && v > te1) te1 = v;
+            }
+            const int te = te1 ? (int)te1 - 1 : 0;
+            StepData se;
+            se.nxt = __shfl_sync(0xffffffffu, sd.nxt, te); se.crt = __shfl_sync(0xffffffffu, sd.crt, te);
+            se.dZ = __shfl_sync(0xffffffffu, sd.dZ, te); se.sh_nxt = __shfl_sync(0xffffffffu, sd.sh_nxt, te);
+            se.sh_crt = __shfl_sync(0xffffffffu, sd.sh_crt, te); se.dsm = __shfl_sync(0xffffffffu, sd.dsm, te);
+            se.sqw = __shfl_sync(0xffffffffu, sd.sqw, te);
+            const uint32_t ni_e = __shfl_sync(0xffffffffu, ni, te), excl_e = __shfl_sync(0xffffffffu, excl, te);
+            // ---- lanes = entries ----
+            if (lane < total) make_record(m, ws, k, l0 + k, lane, se, ni_e - (lane - excl_e), ni_e);
+            if (lane < S) {
+                ws.eoff(k)[lane] = excl;
+                if (lane == S - 1) ws.eoff(k)[S] = excl + ni;
+            }
+        }
+        j -= S;
+        return S;
+    }
+    // ---- a step with more than 32 sub-steps on some line: lanes = sub-entries of step j-1 ----
+    StepData s0;
+    s0.nxt = __shfl_sync(0xffffffffu, sd.nxt, 0); s0.crt = __shfl_sync(0xffffffffu, sd.crt, 0);
+    s0.dZ = __shfl_sync(0xffffffffu, sd.dZ, 0); s0.sh_nxt = __shfl_sync(0xffffffffu, sd.sh_nxt, 0);
+    s0.sh_crt = __shfl_sync(0xffffffffu, sd.sh_crt, 0); s0.dsm = __shfl_sync(0xffffffffu, sd.dsm, 0);
+    s0.sqw = __shfl_sync(0xffffffffu, sd.sqw, 0);
+    bool all_done = true;
+    for (uint32_t k = 0; k < nl; k++) {
+        const uint32_t ni = ws.ni(k)[0], is = *ws.isub(k);
+        const uint32_t rem = ni - is, nemit = rem < 32u ? rem : 32u;
+        if (lane < nemit) make_record(m, ws, k, l0 + k, lane, s0, ni - (is + lane), ni);
+        __syncwarp();
+        if (lane == 0) { ws.eoff(k)[0] = 0; ws.eoff(k)[1] = nemit; *ws.isub(k) = is + nemit; }
+        all_done = all_done && (is + nemit == ni);
+    }
+    if (all_done) {
+        __syncwarp();
+        if (lane < nl) *ws.isub(lane) = 0;
+        j -= 1;
+    }
+    return 1;
+}
+
+__device__ __forceinline__ Rec centre_rec(const DevModel& m, uint32_t o, uint32_t l, double& ie) {
+    const LineRow a = load_row(m, o, l);
+    Rec C;
+    C.shift = 1.0; C.iw = a.inverse_width; C.io = a.opacity; C.sline = ddiv(a.emissivity, a.opacity);
+    C.dsm = __ldg(&m.dshift_max[o]); C.sqw = __ldg(&m.sqrtw_max[o]); C.factor = 0.0; C.p1 = o; C.p2 = o;
+    ie = a.emissivity;
+    return C;
+}
+
+// ---------------------------------------------------------------------------------------------------
 template <int APPROX>
-__global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchView sc, uint32_t nchunks_f) {
-    const unsigned lane = threadIdx.x & 31;
+__global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
+                                                  const FreqChunk* __restrict__ chunks, uint32_t nchunks_f, uint32_t lpw) {
+    const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const size_t nitems = (size_t)pv.no * m.hnrays * nchunks_f;
-    if (item >= nitems) return;
+    if (item >= nitems) return; /* whole warps only */
+    WarpSmem ws;
+    ws.lpw  = lpw;
+    ws.base = wib * (uint32_t)(solve_smem_per_warp(lpw) / 8);
     const uint32_t cf = (uint32_t)(item % nchunks_f);
     const size_t t    = item / nchunks_f;
     const uint32_t rr = (uint32_t)(t % m.hnrays);
     const uint32_t ol = (uint32_t)(t / m.hnrays);
     const uint32_t o  = pv.o0 + ol;
-    const uint32_t f_raw = cf * 32 + lane;
-    const bool active    = f_raw < m.nfreqs;
-    const uint32_t f     = active ? f_raw : m.nfreqs - 1;
-    const uint32_t l     = f / m.nquads;       // line of this frequency bin (f = l*nquads + z, model.cpp:127-146)
-    const uint32_t z     = f - l * m.nquads;
-    const uint32_t ll    = (APPROX == APPROX_ONELINE) ? __ldg(&m.corr_line[f]) : l;
-    const uint32_t ar    = __ldg(&m.antipod[rr]);
-    const double freq    = __ldg(&m.nu[(size_t)o * m.nfreqs + f]);
-    const size_t out     = ((size_t)rr * pv.no + ol) * m.nfreqs + f;
+    const FreqChunk ch = chunks[cf];
+    const bool active  = lane < ch.nf;
+    const uint32_t f   = ch.f0 + (active ? lane : ch.nf - 1);
+    const uint32_t l   = f / m.nquads;       // line of this frequency bin (f = l*nquads + z, model.cpp:127-146)
+    const uint32_t z   = f - l * m.nquads;
+    const uint32_t ks  = l - ch.l0;          // record buffer of this lane's line
+    const uint32_t ll  = (APPROX == APPROX_ONELINE) ? __ldg(&m.corr_line[f]) : l;
+    const uint32_t ar  = __ldg(&m.antipod[rr]);
+    const double freq  = __ldg(&m.nu[(size_t)o * m.nfreqs + f]);
+    const size_t out   = ((size_t)rr * pv.no + ol) * m.nfreqs + f;
 
     const uint32_t len_b = __ldg(&pv.len[(size_t)o * m.nrays + rr]);
     const uint32_t len_f = __ldg(&pv.len[(size_t)o * m.nrays + ar]);
@@ -122,15 +447,22 @@ __global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchV
         return;
     }
 
-    Entry C;
-    C.p1 = o; C.p2 = o; C.factor = 0.0; C.shift = 1.0;
-    double chiC, SC;
-    eval_entry<APPROX>(m, C, ll, freq, chiC, SC);
+    LaneLine L;
+    {
+        const uint32_t pos = __ldg(&m.sorted_pos[l]);
+        L.s_own  = __ldg(&m.line[l]);
+        L.s_prev = pos ? __ldg(&m.sorted_line[pos - 1]) : -CUDART_INF;
+        L.s_next = (pos + 1 < m.nlines) ? __ldg(&m.sorted_line[pos + 1]) : CUDART_INF;
+        L.own    = (APPROX == APPROX_CLOSELINES) || (APPROX == APPROX_ONELINE && ll == l);
+    }
 
     unsigned nlarge = 0, nentries = 1;
-    // results of the two sides
-    double F0 = 0, FI0 = 0, a0 = 0, dt0 = 0, Sn0 = 0, F1 = 0, FI1 = 0, a1 = 0, dt1 = 0, Sc1 = 0;
-    bool lg0 = false, lg1 = false;
+    double F1 = 0, FI1 = 0, a1 = 0, dt1 = 0, Sc1 = 0, SC = 0;
+    bool lg1 = false;
+    {   /* side-0 results wait in shared memory while side 1 runs */
+        double* s0 = ws.side0(lane);
+        s0[0] = 0.0; s0[32] = 0.0; s0[64] = 0.0; s0[96] = 0.0; s0[128] = 0.0; s0[160] = 0.0;
+    }
 
     for (int side = 0; side < 2; side++) {
         const uint32_t r   = side ? ar : rr;
@@ -142,37 +474,59 @@ __global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchV
         SideState st;
         st.haveX = false; st.X_is_end = false; st.large_far = false;
         st.F = st.FI = st.a = st.dtau_far = st.Scurr_far = st.Snext_far = 0.0;
-
-        uint32_t nxt    = __ldg(&pv.nr[off + len - 1]);
-        double sh_nxt   = __ldg(&pv.shift[off + len - 1]);
-        double crit_nxt = __ldg(&m.lrow[(size_t)nxt * m.nlines + l].criterion);
-        for (uint32_t j = len; j-- > 0;) {
-            const double dZj   = __ldg(&pv.dZ[off + j]);
-            const uint32_t crt = j ? __ldg(&pv.nr[off + j - 1]) : o;
-            const double sh_crt = j ? __ldg(&pv.shift[off + j - 1]) : shift0;
-            const double crit_crt = __ldg(&m.lrow[(size_t)crt * m.nlines + l].criterion);
-            const uint32_t ni = n_interp_from_criteria(m, crit_crt, crit_nxt);
-            nentries += ni;
-            double dz = dZj, dshi = 0.0;
-            if (ni > 1) { dz = dZj / ni; dshi = (sh_nxt - sh_crt) / ni; }
-            for (uint32_t i = ni; i >= 1; i--) {
-                Entry Y;
-                Y.p1 = nxt; Y.p2 = crt;
-                Y.factor = (ni > 1) ? 1.0 - ((double)i) / ni : 0.0;
-                Y.shift  = (ni > 1) ? sh_crt + i * dshi : sh_nxt;
-                double chiY, SY;
-                eval_entry<APPROX>(m, Y, ll, freq, chiY, SY);
-                push_entry<APPROX>(m, st, side, Y, chiY, SY, dz, ll, freq, nlarge);
+        __syncwarp();
+        if (lane < ch.nl) *ws.isub(lane) = 0;
+        uint32_t j = len; /* geometric steps not yet expanded (warp-uniform) */
+        bool centre = false;
+        for (;;) {
+            uint32_t S = 1;
+            __syncwarp();
+            if (j > 0) S = produce_window(m, pv, ws, ch.l0, ch.nl, o, off, shift0, j, lane);
+            else centre = true; /* last round: the origin's own entry (nr_[centre] = o, shift_[centre] = 1; solver.tpp:484-485) */
+            __syncwarp();
+            const uint32_t* eo = ws.eoff(ks);
+            const double* rb   = ws.field(ks, 0);
+            if (!centre) nentries += eo[S];
+            for (uint32_t s = 0; s < S; s++) {
+                uint32_t e0 = 0, ns = 1;
+                if (!centre) { e0 = eo[s]; ns = eo[s + 1] - e0; }
+                const uint32_t nmax = __reduce_max_sync(0xffffffffu, ns);
+                for (uint32_t it = 0; it < nmax; it++) {
+                    if (it < ns) {
+                        Rec Y;
+                        double ieY, dzY;
+                        if (centre) {
+                            Y = centre_rec(m, o, l, ieY);
+                            dzY = 0.0;
+                        } else {
+                            const double* q = rb + e0 + it;
+                            Y.shift = q[R_SHIFT * kRecStride]; Y.iw = q[R_IW * kRecStride]; Y.io = q[R_IO * kRecStride];
+                            Y.sline = q[R_SLINE * kRecStride]; Y.dsm = q[R_DSM * kRecStride]; Y.sqw = q[R_SQW * kRecStride];
+                            Y.factor = q[R_FACTOR * kRecStride];
+                            ieY = q[R_IE * kRecStride]; dzY = q[R_DZ * kRecStride];
+                            const uint2 pp = ws.pts()[ks * 32 + e0 + it];
+                            Y.p1 = pp.x; Y.p2 = pp.y;
+                        }
+                        double chiY, SY;
+                        eval_rec<APPROX>(m, L, Y, ieY, ll, freq, chiY, SY);
+                        push_rec<APPROX>(m, L, st, side, Y, chiY, SY, dzY, ll, freq, nlarge);
+                        if (centre) SC = SY;
+                    }
+                }
             }
-            nxt = crt; sh_nxt = sh_crt; crit_nxt = crit_crt;
+            if (centre) break;
         }
-        push_entry<APPROX>(m, st, side, C, chiC, SC, 0.0, ll, freq, nlarge);
-        if (side == 0) { F0 = st.F; FI0 = st.FI; a0 = st.a; dt0 = st.dtau_far; lg0 = st.large_far; Sn0 = st.Snext_far; }
-        else { F1 = st.F; FI1 = st.FI; a1 = st.a; dt1 = st.dtau_far; lg1 = st.large_far; Sc1 = st.Scurr_far; }
+        if (side == 0) {
+            double* s0 = ws.side0(lane);
+            s0[0] = st.F; s0[32] = st.FI; s0[64] = st.a; s0[96] = st.dtau_far; s0[128] = st.Snext_far; s0[160] = st.large_far ? 1.0 : 0.0;
+        } else { F1 = st.F; FI1 = st.FI; a1 = st.a; dt1 = st.dtau_far; lg1 = st.large_far; Sc1 = st.Scurr_far; }
     }
 
     // ---- centre row ----
     double u, Ldiag;
+    const double* s0 = ws.side0(lane);
+    const double F0 = s0[0], FI0 = s0[32], a0 = s0[64], dt0 = s0[96], Sn0 = s0[128];
+    const bool lg0 = s0[160] != 0.0;
     if (len_b && len_f) {
         const double S_c     = lg1 ? Sc1 : SC;
         const double avg     = 0.5 * (dt0 + dt1);
@@ -211,7 +565,7 @@ __global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchV
     const double constante = __ldg(&m.line_A[l]) * __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * w_ang;
     double eta_l, chi_l;
     // NOTE: the reference passes the within-species transition index k as OneLine's line index here (solver.tpp:1798)
-    eta_chi_point<APPROX>(m, o, __ldg(&m.line_k[l]), freq_line, eta_l, chi_l);
+    eta_chi_generic<APPROX>(m, o, o, 0.0, __ldg(&m.line_k[l]), freq_line, eta_l, chi_l);
     const double inverse_chi = 1.0 / chi_l;
     const double frq = freq * 1.0; /* nu(o,f) * shift[centre] */
     const double phi = thermo_profile(m, __ldg(&m.line_invmass[l]), o, freq_line, frq);
@@ -232,7 +586,6 @@ __global__ void __launch_bounds__(128) k_solve(DevModel m, PathView pv, ScratchV
         if (g) atomicAdd(&sc.counters[1], (unsigned long long)g);
     }
 }
-
 // J(o,f) = sum_rr (u * 2) * w[rr] in rr order (solver.tpp:504-506, 515-517); optional copy of u into the full tensor.
 __global__ void k_reduce_J(DevModel m, uint32_t o0, uint32_t no, const double* __restrict__ u, double* __restrict__ J,
                            double* __restrict__ u_full, uint32_t u_o0, uint32_t u_no) {

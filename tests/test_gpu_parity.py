@@ -136,3 +136,33 @@ def test_device_libm_bit_exact(ctx, fn):
     g = got[idx]
     same = (g.view(np.uint32) == want.view(np.uint32)) | (np.isnan(g) & np.isnan(want))
     assert same.all(), f"{fn}: {np.count_nonzero(~same)} mismatches, first x={x[idx][~same][:3]}"
+
+
+def test_ddiv_matches_ieee_division(ctx):
+    """The kernels' scaled division (mgb_device.cuh: ddiv) must equal IEEE-754 round-to-nearest a/b bit for bit:
+    16M random operand pairs over the whole exponent range (incl. the 1e-30..1e-60 magnitudes of SI emissivities),
+    pairs with nearly equal mantissas, exact quotients, zeros, subnormals, inf and NaN."""
+    rng = np.random.default_rng(11)
+    n = 1 << 24
+    mant = lambda k: rng.integers(0, 1 << 52, k, dtype=np.uint64)
+    expo = lambda k, lo, hi: rng.integers(lo, hi, k, dtype=np.uint64) << np.uint64(52)
+    sign = lambda k: rng.integers(0, 2, k, dtype=np.uint64) << np.uint64(63)
+    a = (sign(n) | expo(n, 1, 2047) | mant(n)).view(np.float64)
+    b = (sign(n) | expo(n, 1, 2047) | mant(n)).view(np.float64)
+    # typical magnitudes of the path
+    a2 = np.exp(rng.uniform(-140, 10, n // 4)) * rng.choice([-1.0, 1.0], n // 4)
+    b2 = np.exp(rng.uniform(-140, 10, n // 4))
+    # hard-to-round: mantissas that differ in the last bits, quotients close to 1 and to powers of two
+    m0 = mant(n // 4)
+    a3 = (expo(n // 4, 900, 1100) | m0).view(np.float64)
+    b3 = (expo(n // 4, 900, 1100) | (m0 + rng.integers(0, 4, n // 4, dtype=np.uint64))).view(np.float64)
+    special = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
+                        1e-310, 3.0, 1e300, 1e-300])
+    a4, b4 = [x.ravel() for x in np.meshgrid(special, special)]
+    A = np.concatenate([a, a2, a3, a4, np.ones(1000), rng.integers(1, 1 << 20, 1000).astype(np.float64)])
+    B = np.concatenate([b, b2, b3, b4, rng.uniform(1, 2, 1000), rng.integers(1, 1 << 20, 1000).astype(np.float64)])
+    got = ctx.ddiv(A, B)
+    with np.errstate(all="ignore"):
+        want = A / B
+    same = (got.view(np.uint64) == want.view(np.uint64)) | (np.isnan(got) & np.isnan(want))
+    assert same.all(), f"{np.count_nonzero(~same)} mismatches, first: a={A[~same][:3]} b={B[~same][:3]} got={got[~same][:3]} want={want[~same][:3]}"
