@@ -41,12 +41,15 @@ struct FreqChunk {
     uint32_t l0, nl; // lines l0 .. l0+nl-1 own those bins (f = l*nquads + z), nl <= lpw
 };
 
-constexpr int kRecStride = 34;       // doubles per (field, line) row: 32 entries + 2 pad (distinct banks per line)
-constexpr int kRecFields = 9;        // shift, dz, iw, ie, io, sline, dsm, sqw, factor
-enum { R_SHIFT = 0, R_DZ, R_IW, R_IE, R_IO, R_SLINE, R_DSM, R_SQW, R_FACTOR };
+// Record buffer of one line: kRecFields rows of kRecStride doubles. Slot 0 carries the last record of the
+// previous round (the far end X of the first segment of this round), slots 1..32 hold this round's entries.
+constexpr int kRecStride = 34;       // 33 slots + 1 pad (distinct banks per line)
+constexpr int kRecFields = 10;
+enum { R_SHIFT = 0, R_DZ, R_IW, R_IE, R_IO, R_SLINE, R_DSM, R_SQW, R_FACTOR, R_PTS /* uint2 {nr, nr_interp} */ };
+#define MGB_REC(q, fld) ((q)[(fld) * kRecStride])
 
-constexpr int kWordsPerLine = 102;   // u32 per line: ni[32], excl[32], eoff[36], isub, pad
-constexpr int kLineDoubles  = kRecFields * kRecStride + 32 /* p1,p2 */ + kWordsPerLine / 2;
+constexpr int kWordsPerLine = 104;   // u32 per line: ni[32], excl[32], eoff[36], isub, last, pad
+constexpr int kLineDoubles  = kRecFields * kRecStride + kWordsPerLine / 2;
 
 // bytes of dynamic shared memory per warp
 __host__ __device__ inline size_t solve_smem_per_warp(uint32_t lpw) { return 8 * ((size_t)lpw * kLineDoubles + 6 * 32 /* side-0 results */); }
@@ -57,22 +60,16 @@ extern __shared__ __align__(16) double mgb_smem[];
 struct WarpSmem {
     uint32_t base; // index (in doubles) of this warp's region
     uint32_t lpw;
-    __device__ __forceinline__ double* field(uint32_t k, int fld) const { return mgb_smem + base + (k * kRecFields + fld) * kRecStride; } // [32]
-    __device__ __forceinline__ uint2* pts() const { return reinterpret_cast<uint2*>(mgb_smem + base + lpw * kRecFields * kRecStride); }  // [lpw][32]
+    __device__ __forceinline__ double* rec(uint32_t k) const { return mgb_smem + base + k * (kRecFields * kRecStride); } // [kRecFields][kRecStride]
     __device__ __forceinline__ uint32_t* words(uint32_t k) const {
-        return reinterpret_cast<uint32_t*>(mgb_smem + base + lpw * (kRecFields * kRecStride + 32)) + k * kWordsPerLine;
+        return reinterpret_cast<uint32_t*>(mgb_smem + base + lpw * (kRecFields * kRecStride)) + k * kWordsPerLine;
     }
     __device__ __forceinline__ uint32_t* ni(uint32_t k) const { return words(k); }         // [32] sub-steps of step j-1-lane
     __device__ __forceinline__ uint32_t* excl(uint32_t k) const { return words(k) + 32; }  // [32] exclusive prefix of ni
     __device__ __forceinline__ uint32_t* eoff(uint32_t k) const { return words(k) + 64; }  // [S+1] entry offset of each step in the buffer
     __device__ __forceinline__ uint32_t* isub(uint32_t k) const { return words(k) + 100; } // sub-entries of step j-1 already emitted
+    __device__ __forceinline__ uint32_t* last(uint32_t k) const { return words(k) + 101; } // entries of the previous round (slot to carry)
     __device__ __forceinline__ double* side0(unsigned lane) const { return mgb_smem + base + lpw * kLineDoubles + lane; } // [6][32]
-};
-
-// A ray entry as phase B sees it (registers).
-struct Rec {
-    double shift, iw, io, sline, dsm, sqw, factor;
-    uint32_t p1, p2;
 };
 
 // ---------------------------------------------------------------------------------------------------
@@ -109,138 +106,142 @@ struct LaneLine {
 //   WIN_OTHER : anything else (or NaN)  -> generic path
 enum { WIN_OTHER = 0, WIN_OWN = 1, WIN_EMPTY = 2 };
 __device__ __forceinline__ int window_class(const LaneLine& L, double left, double right) {
-    if (!L.own) return WIN_OTHER;
     const bool prev_below = L.s_prev < left, own_below = L.s_own < left;
     const bool own_above = right < L.s_own, next_above = right < L.s_next;
-    if (prev_below && !own_below && !own_above && next_above) return WIN_OWN;
-    if ((prev_below && own_above) || (own_below && next_above)) return WIN_EMPTY;
-    return WIN_OTHER;
+    const bool is_own   = L.own & prev_below & !own_below & !own_above & next_above;
+    const bool is_empty = L.own & ((prev_below & own_above) | (own_below & next_above));
+    return is_own ? WIN_OWN : (is_empty ? WIN_EMPTY : WIN_OTHER);
 }
 
-// get_eta_and_chi_interpolated at one entry, then S = eta/chi (solver.tpp:2166-2176)
+// compute_S_dtau_line_integrated for the segment between the records X (far) and Y (near) when the window holds
+// exactly the own line (solver.tpp:1878-1912 OneLine, 2012-2111 CloseLines; compute_dtau_single_line :2374-2455).
+// dtau is bit-symmetric under exchanging the two ends (differences and the float erf difference negate exactly,
+// sums and min/max commute), so the roles are fixed here and the caller maps S_atX / S_atY onto the reference's
+// Scurr / Snext according to the side. Out of line: it holds two inlined erff and is taken by a minority of segments.
 template <int APPROX>
-__device__ __forceinline__ void eval_rec(const DevModel& m, const LaneLine& L, const Rec& r, double ie, uint32_t ll, double freq,
-                                         double& chi, double& S) {
-    const double fr = freq * r.shift;
-    double eta;
-    int cls = WIN_OTHER;
-    if (APPROX == APPROX_CLOSELINES) {
-        const double ub = m.max_dist * (fr * r.sqw);
-        cls = window_class(L, fr - ub, fr + ub);
-    } else if (APPROX == APPROX_ONELINE) {
-        cls = L.own ? WIN_OWN : WIN_OTHER;
-    }
-    if (cls == WIN_OWN) {
-        const double prof = gaussian(r.iw, fr - L.s_own);
-        /* the reference accumulates into eta = 0, chi = min_opacity (CloseLines) or adds min_opacity last (OneLine) */
-        eta = 0.0 + prof * ie;
-        if (APPROX == APPROX_ONELINE) chi = (0.0 + prof * r.io) + m.min_opacity;
-        else chi = m.min_opacity + prof * r.io;
-    } else if (cls == WIN_EMPTY) {
-        eta = 0.0; chi = m.min_opacity;
-    } else {
-        eta_chi_generic<APPROX>(m, r.p1, r.p2, r.factor, ll, fr, eta, chi);
-    }
-    S = ddiv(eta, chi);
-}
-
-// compute_S_dtau_line_integrated for the segment c -> n (reference orientation), from the records when the
-// window holds exactly the own line (solver.tpp:1878-1912 OneLine, 2012-2111 CloseLines; compute_dtau_single_line :2374-2455)
-template <int APPROX>
-__device__ __forceinline__ void S_dtau_rec(const DevModel& m, const LaneLine& L, const Rec& c, const Rec& n, uint32_t ll, double currfreq,
-                                           double nextfreq, double dz, double& dtau, double& Scurr, double& Snext) {
-    int cls = WIN_OTHER;
-    if (APPROX == APPROX_CLOSELINES) {
-        double left_freq, right_freq;
-        if (currfreq < nextfreq) { left_freq = currfreq; right_freq = nextfreq; }
-        else { right_freq = currfreq; left_freq = nextfreq; }
-        const double cb = m.max_dist * (right_freq * c.sqw);
-        const double nb = m.max_dist * (right_freq * n.sqw);
-        const double ub = (cb < nb) ? nb : cb;
-        cls = window_class(L, left_freq - ub, right_freq + ub);
-    } else if (APPROX == APPROX_ONELINE) {
-        cls = L.own ? WIN_OWN : WIN_OTHER;
-    }
-    if (cls == WIN_OTHER) {
-        S_dtau_generic<APPROX>(m, c.p1, c.p2, c.factor, n.p1, n.p2, n.factor, ll, currfreq, nextfreq, dz, dtau, Scurr, Snext);
-        return;
-    }
-    if (cls == WIN_EMPTY) { /* no line in reach: sums stay 0, dtau is bounded below by min_opacity*dz (solver.tpp:2095-2110) */
-        double d = 0.0;
-        const double bound_min_dtau = m.min_opacity * dz;
-        if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-        dtau = d; Scurr = 0.0 / d; Snext = 0.0 / d;
-        return;
-    }
-    const double linefreq = L.s_own;
-    const double avg_iw   = (c.iw + n.iw) / 2.0;
+__device__ __noinline__ void line_integrated_own(double min_opacity, double linefreq, double freqX, double freqY, double dz, double iwX,
+                                                 double iwY, double ioX, double ioY, double slX, double slY, double& dtau,
+                                                 double& S_atX, double& S_atY) {
+    const double avg_iw = (iwX + iwY) / 2.0;
+    const double avg_op = (ioX + ioY) / 2.0;
     double ld;
-    if (currfreq == nextfreq) {
-        const double prof   = gaussian(avg_iw, currfreq - linefreq);
-        const double avg_op = (c.io + n.io) / 2.0;
-        ld = dz * (prof * avg_op + m.min_opacity);
+    if (freqX == freqY) {
+        const double prof = gaussian(avg_iw, freqX - linefreq);
+        ld = dz * (prof * avg_op + min_opacity);
     } else {
-        const double next_pos = (linefreq - nextfreq) * avg_iw;
-        const double curr_pos = (linefreq - currfreq) * avg_iw;
-        const double diff_pos = next_pos - curr_pos;
-        const double avg_op   = (n.io + c.io) / 2.0;
-        const float erfdiff   = erff_ool((float)next_pos) - erff_ool((float)curr_pos); /* float subtraction */
+        const double posY = (linefreq - freqY) * avg_iw;
+        const double posX = (linefreq - freqX) * avg_iw;
+        const double diff_pos = posY - posX;
+        const float erfdiff   = mgb_erff((float)posY) - mgb_erff((float)posX); /* float subtraction */
         const double erfterm  = ddiv(avg_op, diff_pos) / 2.0 * (double)erfdiff;
-        ld = dz * (avg_iw * erfterm + m.min_opacity);
+        ld = dz * (avg_iw * erfterm + min_opacity);
     }
-    if (APPROX == APPROX_ONELINE) { dtau = ld; Scurr = c.sline; Snext = n.sline; return; }
-    const double sum_dtau = 0.0 + ld, sum_c = 0.0 + ld * c.sline, sum_n = 0.0 + ld * n.sline;
+    if (APPROX == APPROX_ONELINE) { dtau = ld; S_atX = slX; S_atY = slY; return; }
+    const double sum_dtau = 0.0 + ld, sum_x = 0.0 + ld * slX, sum_y = 0.0 + ld * slY;
     double d = sum_dtau;
-    const double bound_min_dtau = m.min_opacity * dz;
+    const double bound_min_dtau = min_opacity * dz;
     if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-    dtau = d; Scurr = ddiv(sum_c, d); Snext = ddiv(sum_n, d);
+    dtau = d; S_atX = ddiv(sum_x, d); S_atY = ddiv(sum_y, d);
 }
 
-struct SideState {
-    Rec X;            // the far entry of the segment being closed
-    double chiX, SX;  // eta/chi evaluation at X
-    double dzX;       // length of the segment between X and its nearer neighbour
-    double dtau_far;  // optical depth of X's far segment
-    double Scurr_far, Snext_far; // line-integrated sources of that segment (reference orientation)
-    double F, FI, a;  // Rybicki-Hummer F (FF or GG), 1/(1+F), eliminated source (Su)
+struct SweepState {
+    double chiX, SX;     // eta/chi evaluation at the far entry X of the open segment
+    double dtau_far;     // optical depth of X's far segment
+    double SatY_far;     // line-integrated source of that segment at its near end (= at X)
+    double F, FI, a;     // Rybicki-Hummer F (FF or GG), 1/(1+F), eliminated source (Su)
     bool haveX, X_is_end, large_far;
 };
 
-// Close the segment between the far entry st.X and the nearer entry Y, then advance.
-// side 0: reference orientation curr = X, next = Y.  side 1: curr = Y, next = X.
+// One entry of the sweep: evaluate eta, chi, S at the record Y = q[0] (get_eta_and_chi_interpolated, then S = eta/chi,
+// solver.tpp:2166-2176), close the segment between the previous record X = q[-1] and Y (compute_source_dtau,
+// :2139-2186) and eliminate X's row. side 0: reference orientation curr = X, next = Y.  side 1: curr = Y, next = X.
 template <int APPROX>
-__device__ __forceinline__ void push_rec(const DevModel& m, const LaneLine& L, SideState& st, int side, const Rec& Y, double chiY,
-                                         double SY, double dzY, uint32_t ll, double freq, unsigned& nlarge) {
+__device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L, SweepState& st, int side, const double* q, uint32_t ll,
+                                           double freq, unsigned& nlarge) {
+    const double shY = MGB_REC(q, R_SHIFT);
+    const double frY = freq * shY;
+    double chiY, SY;
+    {
+        int cls = WIN_OTHER;
+        if (APPROX == APPROX_CLOSELINES) {
+            const double ub = m.max_dist * (frY * MGB_REC(q, R_SQW));
+            cls = window_class(L, frY - ub, frY + ub);
+        } else if (APPROX == APPROX_ONELINE) {
+            cls = L.own ? WIN_OWN : WIN_OTHER;
+        }
+        if (cls == WIN_OWN) {
+            const double prof = gaussian(MGB_REC(q, R_IW), frY - L.s_own);
+            /* the reference accumulates into eta = 0, chi = min_opacity (CloseLines) or adds min_opacity last (OneLine) */
+            const double eta = 0.0 + prof * MGB_REC(q, R_IE);
+            if (APPROX == APPROX_ONELINE) chiY = (0.0 + prof * MGB_REC(q, R_IO)) + m.min_opacity;
+            else chiY = m.min_opacity + prof * MGB_REC(q, R_IO);
+            SY = ddiv(eta, chiY);
+        } else if (cls == WIN_EMPTY) {
+            chiY = m.min_opacity;
+            SY   = ddiv(0.0, chiY); /* eta = 0 */
+        } else {
+            const uint2 pp = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
+            double eta;
+            eta_chi_generic<APPROX>(m, pp.x, pp.y, MGB_REC(q, R_FACTOR), ll, frY, eta, chiY);
+            SY = ddiv(eta, chiY);
+        }
+    }
     if (st.haveX) {
-        const Rec& c = side ? Y : st.X;
-        const Rec& n = side ? st.X : Y;
+        const double* x = q - 1;
+        const double shX = MGB_REC(x, R_SHIFT), dzX = MGB_REC(x, R_DZ);
         // compute_source_dtau (solver.tpp:2139-2186)
-        const double dshift_abs = fabs(n.shift - c.shift);
-        const double da = c.dsm, db = n.dsm;
-        const double dshift_max = (db < da) ? db : da;
-        double dtau, Scurr = 0.0, Snext = 0.0;
+        const double dshift_abs = fabs(shY - shX);
+        const double dX = MGB_REC(x, R_DSM), dY = MGB_REC(q, R_DSM);
+        const double dshift_max = (dY < dX) ? dY : dX;
+        double dtau, S_atX = 0.0, S_atY = 0.0;
         const bool large = dshift_abs > dshift_max;
         if (large) {
-            S_dtau_rec<APPROX>(m, L, c, n, ll, freq * c.shift, freq * n.shift, st.dzX, dtau, Scurr, Snext);
             nlarge++;
+            const double frX = freq * shX;
+            int cls = WIN_OTHER;
+            if (APPROX == APPROX_CLOSELINES) {
+                const double left_freq = (frX < frY) ? frX : frY, right_freq = (frX < frY) ? frY : frX;
+                const double bX = m.max_dist * (right_freq * MGB_REC(x, R_SQW));
+                const double bY = m.max_dist * (right_freq * MGB_REC(q, R_SQW));
+                const double ub = (bX < bY) ? bY : bX;
+                cls = window_class(L, left_freq - ub, right_freq + ub);
+            } else if (APPROX == APPROX_ONELINE) {
+                cls = L.own ? WIN_OWN : WIN_OTHER;
+            }
+            if (cls == WIN_OWN) {
+                line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW), MGB_REC(x, R_IO),
+                                            MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE), dtau, S_atX, S_atY);
+            } else if (cls == WIN_EMPTY) {
+                /* no line in reach: sums stay 0, dtau is bounded below by min_opacity*dz (solver.tpp:2095-2110) */
+                double d = 0.0;
+                const double bound_min_dtau = m.min_opacity * dzX;
+                if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
+                dtau = d; S_atX = ddiv(0.0, d); S_atY = S_atX;
+            } else {
+                const uint2 pX = *reinterpret_cast<const uint2*>(&MGB_REC(x, R_PTS)), pY = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
+                const double fX = MGB_REC(x, R_FACTOR), fY = MGB_REC(q, R_FACTOR);
+                if (side == 0) S_dtau_generic<APPROX>(m, pX.x, pX.y, fX, pY.x, pY.y, fY, ll, frX, frY, dzX, dtau, S_atX, S_atY);
+                else S_dtau_generic<APPROX>(m, pY.x, pY.y, fY, pX.x, pX.y, fX, ll, frY, frX, dzX, dtau, S_atY, S_atX);
+            }
         } else {
-            const double chic = side ? chiY : st.chiX, chin = side ? st.chiX : chiY;
-            dtau = 0.5 * (chic + chin) * st.dzX;
+            dtau = 0.5 * (st.chiX + chiY) * dzX;
         }
         if (st.X_is_end) {
             // boundary row (solver.tpp:2240-2262 for `first`, 2283-2297 mirrored for `last`)
-            const double S0 = large ? (side ? Snext : Scurr) : st.SX;
+            const double S0  = large ? S_atX : st.SX;
             const double inv = ddiv(1.0, dtau);
             const double Cb  = 2.0 * inv * inv;
             const double Bm  = 1.0 + 2.0 * inv;
             const double B   = Bm + Cb;
-            const double Ib  = boundary_intensity(m, st.X.p1, freq * st.X.shift);
+            const uint2 pX   = *reinterpret_cast<const uint2*>(&MGB_REC(x, R_PTS));
+            const double Ib  = boundary_intensity(m, pX.x, freq * shX);
             st.a  = ddiv(S0 + 2.0 * Ib * inv, B);
             st.F  = 0.5 * Bm * dtau * dtau;
             st.FI = ddiv(1.0, 1.0 + st.F);
         } else {
-            // interior row (solver.tpp:2264-2281; mirrored 2306-2311)
-            const double Sx = side ? (st.large_far ? st.Scurr_far : st.SX) : (large ? Scurr : st.SX);
+            // interior row (solver.tpp:2264-2281; mirrored 2306-2311): the row's source is the line-integrated one of the
+            // segment in which X is `curr` (the near segment on side 0, the far one on side 1)
+            const double Sx = side ? (st.large_far ? st.SatY_far : st.SX) : (large ? S_atX : st.SX);
             const double avg     = 0.5 * (st.dtau_far + dtau);
             const double invFar  = avg * st.dtau_far;
             const double invNear = avg * dtau;
@@ -251,14 +252,13 @@ __device__ __forceinline__ void push_rec(const DevModel& m, const LaneLine& L, S
         }
         st.dtau_far  = dtau;
         st.large_far = large;
-        st.Scurr_far = Scurr;
-        st.Snext_far = Snext;
+        st.SatY_far  = S_atY;
         st.X_is_end  = false;
     } else {
         st.haveX    = true;
         st.X_is_end = true;
     }
-    st.X = Y; st.chiX = chiY; st.SX = SY; st.dzX = dzY;
+    st.chiX = chiY; st.SX = SY;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -271,8 +271,8 @@ struct StepData { // one geometric step crt -> nxt of the cached path (independe
     double dZ, sh_nxt, sh_crt, dsm, sqw;
 };
 
-__device__ __forceinline__ void make_record(const DevModel& m, const WarpSmem& ws, uint32_t k, uint32_t l, uint32_t slot, const StepData& sd,
-                                            uint32_t i, uint32_t ni) {
+__device__ __forceinline__ void make_record(const DevModel& m, double* r /* record slot */, uint32_t l, const StepData& sd, uint32_t i,
+                                            uint32_t ni) {
     double dz = sd.dZ, factor = 0.0, shift = sd.sh_nxt;
     if (ni > 1) {
         dz = sd.dZ / ni;
@@ -290,24 +290,35 @@ __device__ __forceinline__ void make_record(const DevModel& m, const WarpSmem& w
         io    = interp_log(a.opacity, b.opacity, factor);
         sline = interp_log(sline, ddiv(b.emissivity, b.opacity), factor);
     }
-    double* r = ws.field(k, 0) + slot;
-    r[R_SHIFT * kRecStride]  = shift;
-    r[R_DZ * kRecStride]     = dz;
-    r[R_IW * kRecStride]     = iw;
-    r[R_IE * kRecStride]     = ie;
-    r[R_IO * kRecStride]     = io;
-    r[R_SLINE * kRecStride]  = sline;
-    r[R_DSM * kRecStride]    = sd.dsm;
-    r[R_SQW * kRecStride]    = sd.sqw;
-    r[R_FACTOR * kRecStride] = factor;
-    ws.pts()[k * 32 + slot]  = make_uint2(sd.nxt, sd.crt);
+    MGB_REC(r, R_SHIFT)  = shift;
+    MGB_REC(r, R_DZ)     = dz;
+    MGB_REC(r, R_IW)     = iw;
+    MGB_REC(r, R_IE)     = ie;
+    MGB_REC(r, R_IO)     = io;
+    MGB_REC(r, R_SLINE)  = sline;
+    MGB_REC(r, R_DSM)    = sd.dsm;
+    MGB_REC(r, R_SQW)    = sd.sqw;
+    MGB_REC(r, R_FACTOR) = factor;
+    *reinterpret_cast<uint2*>(&MGB_REC(r, R_PTS)) = make_uint2(sd.nxt, sd.crt);
+}
+
+// Before a round overwrites the buffers: keep each line's last record in slot 0 (it is the far end of the next segment).
+__device__ __forceinline__ void carry_last_records(const WarpSmem& ws, uint32_t nl, unsigned lane) {
+    for (uint32_t k = 0; k < nl; k++) {
+        const uint32_t last = *ws.last(k);
+        if (last && lane < kRecFields) {
+            double* row = ws.rec(k) + lane * kRecStride;
+            row[0] = row[last];
+        }
+    }
+    __syncwarp();
 }
 
 // Expand the next geometric steps j-1, j-2, ... of the half-ray for all nl lines of the warp. Returns the number S of
-// steps whose entries are now in the record buffers (eoff(k)[0..S] = entry offsets per step of line k); all lines
-// advance by the SAME steps so that phase B runs in lock-step over segments (uniform large/small-shift branch).
-// S is limited by the 32 record slots per line. A single step with more than 32 sub-steps on some line is
-// emitted 32 entries at a time (isub cursors) and reported as S = 1 with j unchanged until every line is through.
+// steps whose entries are now in the record buffers (eoff(k)[0..S] = entry offsets per step of line k; entry e sits in
+// slot 1+e); all lines advance by the SAME steps so that phase B runs in lock-step over segments (uniform
+// large/small-shift branch). S is limited by the 32 entry slots per line. A single step with more than 32 sub-steps on
+// some line is emitted 32 entries at a time (isub cursors) and reported as S = 1 with j unchanged until every line is through.
 __device__ __forceinline__ uint32_t produce_window(const DevModel& m, const PathView& pv, const WarpSmem& ws, uint32_t l0, uint32_t nl,
                                                    uint32_t o, unsigned long long off, double shift0, uint32_t& j, unsigned lane) {
     // ---- lanes = steps ----
@@ -369,10 +380,10 @@ __device__ __forceinline__ uint32_t produce_window(const DevModel& m, const Path
             se.sqw = __shfl_sync(0xffffffffu, sd.sqw, te);
             const uint32_t ni_e = __shfl_sync(0xffffffffu, ni, te), excl_e = __shfl_sync(0xffffffffu, excl, te);
             // ---- lanes = entries ----
-            if (lane < total) make_record(m, ws, k, l0 + k, lane, se, ni_e - (lane - excl_e), ni_e);
+            if (lane < total) make_record(m, ws.rec(k) + 1 + lane, l0 + k, se, ni_e - (lane - excl_e), ni_e);
             if (lane < S) {
                 ws.eoff(k)[lane] = excl;
-                if (lane == S - 1) ws.eoff(k)[S] = excl + ni;
+                if (lane == S - 1) { ws.eoff(k)[S] = excl + ni; *ws.last(k) = excl + ni; }
             }
         }
         j -= S;
@@ -388,9 +399,9 @@ __device__ __forceinline__ uint32_t produce_window(const DevModel& m, const Path
     for (uint32_t k = 0; k < nl; k++) {
         const uint32_t ni = ws.ni(k)[0], is = *ws.isub(k);
         const uint32_t rem = ni - is, nemit = rem < 32u ? rem : 32u;
-        if (lane < nemit) make_record(m, ws, k, l0 + k, lane, s0, ni - (is + lane), ni);
+        if (lane < nemit) make_record(m, ws.rec(k) + 1 + lane, l0 + k, s0, ni - (is + lane), ni);
         __syncwarp();
-        if (lane == 0) { ws.eoff(k)[0] = 0; ws.eoff(k)[1] = nemit; *ws.isub(k) = is + nemit; }
+        if (lane == 0) { ws.eoff(k)[0] = 0; ws.eoff(k)[1] = nemit; *ws.isub(k) = is + nemit; *ws.last(k) = nemit; }
         all_done = all_done && (is + nemit == ni);
     }
     if (all_done) {
@@ -401,13 +412,15 @@ __device__ __forceinline__ uint32_t produce_window(const DevModel& m, const Path
     return 1;
 }
 
-__device__ __forceinline__ Rec centre_rec(const DevModel& m, uint32_t o, uint32_t l, double& ie) {
-    const LineRow a = load_row(m, o, l);
-    Rec C;
-    C.shift = 1.0; C.iw = a.inverse_width; C.io = a.opacity; C.sline = ddiv(a.emissivity, a.opacity);
-    C.dsm = __ldg(&m.dshift_max[o]); C.sqw = __ldg(&m.sqrtw_max[o]); C.factor = 0.0; C.p1 = o; C.p2 = o;
-    ie = a.emissivity;
-    return C;
+// The origin's own entry (nr_[centre] = o, shift_[centre] = 1; solver.tpp:484-485) as the single record of the last round.
+__device__ __forceinline__ void produce_centre(const DevModel& m, const WarpSmem& ws, uint32_t l0, uint32_t nl, uint32_t o, unsigned lane) {
+    if (lane < nl) {
+        StepData sd;
+        sd.nxt = o; sd.crt = o; sd.dZ = 0.0; sd.sh_nxt = 1.0; sd.sh_crt = 1.0;
+        sd.dsm = __ldg(&m.dshift_max[o]); sd.sqw = __ldg(&m.sqrtw_max[o]);
+        make_record(m, ws.rec(lane) + 1, l0 + lane, sd, 1, 1);
+        ws.eoff(lane)[0] = 0; ws.eoff(lane)[1] = 1; *ws.last(lane) = 1;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -456,13 +469,15 @@ __global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevMod
         L.own    = (APPROX == APPROX_CLOSELINES) || (APPROX == APPROX_ONELINE && ll == l);
     }
 
-    unsigned nlarge = 0, nentries = 1;
+    unsigned nlarge = 0, nentries = 1; /* the origin's own entry */
     double F1 = 0, FI1 = 0, a1 = 0, dt1 = 0, Sc1 = 0, SC = 0;
     bool lg1 = false;
     {   /* side-0 results wait in shared memory while side 1 runs */
         double* s0 = ws.side0(lane);
         s0[0] = 0.0; s0[32] = 0.0; s0[64] = 0.0; s0[96] = 0.0; s0[128] = 0.0; s0[160] = 0.0;
     }
+    const double* rb   = ws.rec(ks) + 1; /* entry e of this lane's line */
+    const uint32_t* eo = ws.eoff(ks);
 
     for (int side = 0; side < 2; side++) {
         const uint32_t r   = side ? ar : rr;
@@ -471,55 +486,35 @@ __global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevMod
         const size_t hr = (size_t)ol * m.nrays + r;
         const unsigned long long off = __ldg(&pv.poff[hr]);
         const double shift0 = __ldg(&pv.shift0[hr]);
-        SideState st;
+        SweepState st;
         st.haveX = false; st.X_is_end = false; st.large_far = false;
-        st.F = st.FI = st.a = st.dtau_far = st.Scurr_far = st.Snext_far = 0.0;
+        st.chiX = st.SX = st.F = st.FI = st.a = st.dtau_far = st.SatY_far = 0.0;
         __syncwarp();
-        if (lane < ch.nl) *ws.isub(lane) = 0;
+        if (lane < ch.nl) { *ws.isub(lane) = 0; *ws.last(lane) = 0; }
+        __syncwarp();
         uint32_t j = len; /* geometric steps not yet expanded (warp-uniform) */
-        bool centre = false;
         for (;;) {
             uint32_t S = 1;
+            const bool centre = (j == 0);
+            carry_last_records(ws, ch.nl, lane);
+            if (!centre) S = produce_window(m, pv, ws, ch.l0, ch.nl, o, off, shift0, j, lane);
+            else produce_centre(m, ws, ch.l0, ch.nl, o, lane);
             __syncwarp();
-            if (j > 0) S = produce_window(m, pv, ws, ch.l0, ch.nl, o, off, shift0, j, lane);
-            else centre = true; /* last round: the origin's own entry (nr_[centre] = o, shift_[centre] = 1; solver.tpp:484-485) */
-            __syncwarp();
-            const uint32_t* eo = ws.eoff(ks);
-            const double* rb   = ws.field(ks, 0);
             if (!centre) nentries += eo[S];
             for (uint32_t s = 0; s < S; s++) {
-                uint32_t e0 = 0, ns = 1;
-                if (!centre) { e0 = eo[s]; ns = eo[s + 1] - e0; }
+                const uint32_t e0 = eo[s], ns = eo[s + 1] - e0;
                 const uint32_t nmax = __reduce_max_sync(0xffffffffu, ns);
-                for (uint32_t it = 0; it < nmax; it++) {
-                    if (it < ns) {
-                        Rec Y;
-                        double ieY, dzY;
-                        if (centre) {
-                            Y = centre_rec(m, o, l, ieY);
-                            dzY = 0.0;
-                        } else {
-                            const double* q = rb + e0 + it;
-                            Y.shift = q[R_SHIFT * kRecStride]; Y.iw = q[R_IW * kRecStride]; Y.io = q[R_IO * kRecStride];
-                            Y.sline = q[R_SLINE * kRecStride]; Y.dsm = q[R_DSM * kRecStride]; Y.sqw = q[R_SQW * kRecStride];
-                            Y.factor = q[R_FACTOR * kRecStride];
-                            ieY = q[R_IE * kRecStride]; dzY = q[R_DZ * kRecStride];
-                            const uint2 pp = ws.pts()[ks * 32 + e0 + it];
-                            Y.p1 = pp.x; Y.p2 = pp.y;
-                        }
-                        double chiY, SY;
-                        eval_rec<APPROX>(m, L, Y, ieY, ll, freq, chiY, SY);
-                        push_rec<APPROX>(m, L, st, side, Y, chiY, SY, dzY, ll, freq, nlarge);
-                        if (centre) SC = SY;
-                    }
-                }
+                for (uint32_t it = 0; it < nmax; it++)
+                    if (it < ns) sweep_step<APPROX>(m, L, st, side, rb + e0 + it, ll, freq, nlarge);
             }
+            __syncwarp();
             if (centre) break;
         }
+        SC = st.SX; /* source function at the origin */
         if (side == 0) {
             double* s0 = ws.side0(lane);
-            s0[0] = st.F; s0[32] = st.FI; s0[64] = st.a; s0[96] = st.dtau_far; s0[128] = st.Snext_far; s0[160] = st.large_far ? 1.0 : 0.0;
-        } else { F1 = st.F; FI1 = st.FI; a1 = st.a; dt1 = st.dtau_far; lg1 = st.large_far; Sc1 = st.Scurr_far; }
+            s0[0] = st.F; s0[32] = st.FI; s0[64] = st.a; s0[96] = st.dtau_far; s0[128] = st.SatY_far; s0[160] = st.large_far ? 1.0 : 0.0;
+        } else { F1 = st.F; FI1 = st.FI; a1 = st.a; dt1 = st.dtau_far; lg1 = st.large_far; Sc1 = st.SatY_far; }
     }
 
     // ---- centre row ----
