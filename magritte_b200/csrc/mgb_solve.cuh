@@ -178,7 +178,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             SY = ddiv(eta, chiY);
         } else if (cls == WIN_EMPTY) {
             chiY = m.min_opacity;
-            SY   = ddiv(0.0, chiY); /* eta = 0 */
+            SY   = (chiY > 0.0 && chiY < CUDART_INF) ? 0.0 : 0.0 / chiY; /* eta = 0 */
         } else {
             const uint2 pp = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
             double eta;
