@@ -291,8 +291,10 @@ def run_b200(args):
             ctx.set_line_state(h_e, h_o, h_w, h_t)
             ctx.run(approx, o_range)
             ctx.allgather()
-            ctx.lib.mgb_get_J(ctx._ctx, 0, N, h_J.ctypes.data)
-            ctx.lib.mgb_get_lambda(ctx._ctx, 0, N, h_lv.ctypes.data, h_lc.ctypes.data)
+            import ctypes as C
+            ctx._check(ctx.lib.mgb_get_J(ctx._ctx, C.c_uint32(0), C.c_uint32(N), C.c_void_p(h_J.ctypes.data)), "mgb_get_J")
+            ctx._check(ctx.lib.mgb_get_lambda(ctx._ctx, C.c_uint32(0), C.c_uint32(N), C.c_void_p(h_lv.ctypes.data),
+                                              C.c_void_p(h_lc.ctypes.data)), "mgb_get_lambda")
         return float(h_J[0, 0])
 
     step_e2e()

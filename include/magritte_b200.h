@@ -145,6 +145,9 @@ int mgb_nccl_unique_id(void* id128);
 int mgb_comm_init(mgb_ctx* ctx, int nranks, int rank, const void* id128);
 /* Even split of [0,npoints) into nranks contiguous ranges of equal element count (the last padded). */
 int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end);
+/* The same split without a context (pure host arithmetic): rank r owns rows [r*per, min((r+1)*per, npoints)), per = ceil(npoints/nranks);
+ * the all-gather moves `per` rows per rank, the result buffers are padded to per*nranks rows. */
+int mgb_partition_rows(uint32_t npoints, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end, uint32_t* rows_per_rank);
 /* In-place ncclAllGather of the J and Lambda slices every rank computed for its mgb_partition range. */
 int mgb_allgather_results(mgb_ctx* ctx);
 

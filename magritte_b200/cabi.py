@@ -11,13 +11,13 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmagritte_b200.so")
+LIB_PATH = os.environ.get("MGB_LIB") or os.path.join(_HERE, "lib", "libmagritte_b200.so")  # MGB_LIB: A/B builds of the same library
 
 EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
-    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition",
+    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_rows",
     "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
 ]
 
@@ -57,6 +57,14 @@ def load():
         _lib.mgb_destroy.restype = None
         _lib.mgb_destroy.argtypes = [C.c_void_p]
     return _lib
+
+
+def partition_rows(npoints, nranks, rank):
+    """(o_begin, o_end, rows_per_rank) of mgb_partition_rows: host arithmetic, needs no GPU."""
+    a, b, per = C.c_uint32(), C.c_uint32(), C.c_uint32()
+    if load().mgb_partition_rows(C.c_uint32(npoints), C.c_int(nranks), C.c_int(rank), C.byref(a), C.byref(b), C.byref(per)) != 0:
+        raise ValueError("mgb_partition_rows: invalid arguments")
+    return a.value, b.value, per.value
 
 
 class MgbError(RuntimeError):

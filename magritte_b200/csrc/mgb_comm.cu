@@ -64,13 +64,19 @@ extern "C" int mgb_comm_init(mgb_ctx* ctx, int nranks, int rank, const void* id1
 
 static uint32_t rows_per_rank(uint32_t npoints, int nranks) { return (npoints + (uint32_t)nranks - 1) / (uint32_t)nranks; }
 
-extern "C" int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
-    if (!ctx || !o_begin || !o_end || nranks < 1 || rank < 0 || rank >= nranks || !ctx->have_geometry) return MGB_EINVAL;
-    const uint32_t N = ctx->m.npoints, per = rows_per_rank(N, nranks);
+extern "C" int mgb_partition_rows(uint32_t npoints, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end, uint32_t* rows_per_rank_out) {
+    if (!o_begin || !o_end || nranks < 1 || rank < 0 || rank >= nranks) return MGB_EINVAL;
+    const uint32_t N = npoints, per = rows_per_rank(N, nranks);
     const uint64_t b = (uint64_t)per * rank, e = b + per;
     *o_begin = (uint32_t)(b < N ? b : N);
     *o_end   = (uint32_t)(e < N ? e : N);
+    if (rows_per_rank_out) *rows_per_rank_out = per;
     return MGB_OK;
+}
+
+extern "C" int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
+    if (!ctx || !ctx->have_geometry) return MGB_EINVAL;
+    return mgb_partition_rows(ctx->m.npoints, nranks, rank, o_begin, o_end, nullptr);
 }
 
 extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
