@@ -224,7 +224,7 @@ def run_b200(args):
         uid = [ctx.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(world, rank, uid[0])
-    o_range = ctx.partition(world, rank)
+    o_range = ctx.partition(world, rank, balanced=True)
     N, H, F, L = int(flat["npoints"]), int(flat["hnrays"]), int(flat["nfreqs"]), int(flat["nlines"])
     solves_total = N * H * F
 

@@ -144,11 +144,14 @@ int mgb_timer_stop(mgb_ctx* ctx, float* ms);
 int mgb_nccl_unique_id(void* id128);
 int mgb_comm_init(mgb_ctx* ctx, int nranks, int rank, const void* id128);
 /* Even split of [0,npoints) into nranks contiguous ranges of equal element count (the last padded). */
-int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end);
+int mgb_partition(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end);
+/* Contiguous ranges of equal predicted cost (sum of geometric ray lengths per origin, from the cached count pass). */
+int mgb_partition_balanced(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end);
 /* The same split without a context (pure host arithmetic): rank r owns rows [r*per, min((r+1)*per, npoints)), per = ceil(npoints/nranks);
  * the all-gather moves `per` rows per rank, the result buffers are padded to per*nranks rows. */
 int mgb_partition_rows(uint32_t npoints, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end, uint32_t* rows_per_rank);
-/* In-place ncclAllGather of the J and Lambda slices every rank computed for its mgb_partition range. */
+/* In-place all-gather (one grouped ncclBroadcast per owner, so ranges may differ in size) of the J and Lambda slices every rank
+ * computed for its mgb_partition / mgb_partition_balanced range. */
 int mgb_allgather_results(mgb_ctx* ctx);
 
 /* ---- test hooks ------------------------------------------------------------------------------ */

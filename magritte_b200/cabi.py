@@ -17,7 +17,7 @@ EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
-    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_rows",
+    "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
     "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
 ]
 
@@ -229,9 +229,10 @@ class Context:
     def comm_init(self, nranks, rank, uid):
         self._check(self.lib.mgb_comm_init(self._ctx, C.c_int(nranks), C.c_int(rank), C.c_char_p(uid)), "mgb_comm_init")
 
-    def partition(self, nranks, rank):
+    def partition(self, nranks, rank, balanced=False):
         a, b = C.c_uint32(), C.c_uint32()
-        self._check(self.lib.mgb_partition(self._ctx, C.c_int(nranks), C.c_int(rank), C.byref(a), C.byref(b)), "mgb_partition")
+        fn = self.lib.mgb_partition_balanced if balanced else self.lib.mgb_partition
+        self._check(fn(self._ctx, C.c_int(nranks), C.c_int(rank), C.byref(a), C.byref(b)), "mgb_partition")
         return a.value, b.value
 
     def allgather(self):

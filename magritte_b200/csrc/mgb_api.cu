@@ -388,6 +388,30 @@ cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc
 
 } // namespace
 
+// Contiguous origin ranges of equal predicted cost: cost(o) = sum over rays of the geometric ray length (the count pass), plus one
+// entry per ray for the origin itself. Every rank computes the same bounds from the same replicated geometry.
+extern "C" int mgb_partition_balanced(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
+    if (!ctx || !o_begin || !o_end || nranks < 1 || rank < 0 || rank >= nranks) return MGB_EINVAL;
+    if (!(ctx->have_geometry && ctx->have_thermo && ctx->have_lines)) return ctx->fail(MGB_ESTATE, "mgb_partition_balanced: model incomplete");
+    cudaSetDevice(ctx->device);
+    const uint32_t N = ctx->m.npoints;
+    uint32_t launches = 0;
+    MGB_TRY(refresh_points(ctx));
+    MGB_TRY(ensure_lens(ctx, 0, N, nullptr, launches));
+    std::vector<unsigned long long> pre(N + 1, 0);
+    for (uint32_t o = 0; o < N; o++) pre[o + 1] = pre[o] + ctx->origin_steps[o] + ctx->m.nrays;
+    ctx->part_bounds.assign(nranks + 1, N);
+    ctx->part_bounds[0] = 0;
+    for (int r = 1; r < nranks; r++) {
+        const unsigned long long target = pre[N] / nranks * r;
+        ctx->part_bounds[r] = (uint32_t)(std::lower_bound(pre.begin(), pre.end(), target) - pre.begin());
+        if (ctx->part_bounds[r] < ctx->part_bounds[r - 1]) ctx->part_bounds[r] = ctx->part_bounds[r - 1];
+        if (ctx->part_bounds[r] > N) ctx->part_bounds[r] = N;
+    }
+    *o_begin = ctx->part_bounds[rank]; *o_end = ctx->part_bounds[rank + 1];
+    return MGB_OK;
+}
+
 extern "C" int mgb_invalidate_paths(mgb_ctx* ctx) {
     if (!ctx) return MGB_EINVAL;
     cudaSetDevice(ctx->device);

@@ -19,6 +19,7 @@ struct Nccl {
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int)                            = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t)                                                      = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t)         = nullptr;
+    ncclResult_t (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t)    = nullptr;
     ncclResult_t (*GroupStart)()                                                                 = nullptr;
     ncclResult_t (*GroupEnd)()                                                                   = nullptr;
     const char* (*GetErrorString)(ncclResult_t)                                                  = nullptr;
@@ -30,7 +31,7 @@ struct Nccl {
         *(void**)(&f) = dlsym(h, name);                            \
         if (!f) { err = std::string("dlsym ") + name; return false; }
         SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
-        SYM(AllGather, "ncclAllGather") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+        SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
         SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
         return true;
@@ -74,8 +75,14 @@ extern "C" int mgb_partition_rows(uint32_t npoints, int nranks, int rank, uint32
     return MGB_OK;
 }
 
-extern "C" int mgb_partition(const mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
-    if (!ctx || !ctx->have_geometry) return MGB_EINVAL;
+extern "C" int mgb_partition(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
+    if (!ctx || !ctx->have_geometry || nranks < 1) return MGB_EINVAL;
+    ctx->part_bounds.assign(nranks + 1, ctx->m.npoints);
+    for (int r = 0; r < nranks; r++) {
+        uint32_t a, b;
+        mgb_partition_rows(ctx->m.npoints, nranks, r, &a, &b, nullptr);
+        ctx->part_bounds[r] = a;
+    }
     return mgb_partition_rows(ctx->m.npoints, nranks, rank, o_begin, o_end, nullptr);
 }
 
@@ -86,20 +93,22 @@ extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
     if (!ctx->J.p) return ctx->fail(MGB_ESTATE, "mgb_allgather_results: no results");
     cudaSetDevice(ctx->device);
     const mgb::DevModel& m = ctx->m;
-    const uint32_t per = rows_per_rank(m.npoints, ctx->nranks);
-    const size_t need_rows = (size_t)per * ctx->nranks;
-    if (ctx->J.bytes < 8 * need_rows * m.nfreqs || ctx->lam_val.bytes < 8 * need_rows * m.nlines || ctx->lam_cnt.bytes < 4 * need_rows * m.nlines)
-        return ctx->fail(MGB_ESTATE, "mgb_allgather_results: result buffers are not padded for %d ranks (run after mgb_comm_init)", ctx->nranks);
+    if ((int)ctx->part_bounds.size() != ctx->nranks + 1)
+        return ctx->fail(MGB_ESTATE, "mgb_allgather_results: call mgb_partition or mgb_partition_balanced with nranks = %d first", ctx->nranks);
     ncclComm_t comm = (ncclComm_t)ctx->comm;
-    // in place: every rank's slice already sits at rank*per rows of the full-size buffers
+    // all-gather with per-rank row counts, in place: every rank's slice already sits at its global rows, one broadcast per owner
     ncclResult_t r = g_nccl.GroupStart();
     char* J = (char*)ctx->J.p; char* lv = (char*)ctx->lam_val.p; char* lc = (char*)ctx->lam_cnt.p;
-    const size_t nJ = (size_t)per * m.nfreqs, nL = (size_t)per * m.nlines;
-    if (!r) r = g_nccl.AllGather(J + 8 * nJ * ctx->rank, J, nJ, ncclFloat64, comm, ctx->stream);
-    if (!r) r = g_nccl.AllGather(lv + 8 * nL * ctx->rank, lv, nL, ncclFloat64, comm, ctx->stream);
-    if (!r) r = g_nccl.AllGather(lc + 4 * nL * ctx->rank, lc, nL, ncclUint32, comm, ctx->stream);
+    for (int root = 0; root < ctx->nranks && !r; root++) {
+        const size_t o0 = ctx->part_bounds[root], rows = ctx->part_bounds[root + 1] - o0;
+        if (!rows) continue;
+        const size_t nJ = rows * m.nfreqs, nL = rows * m.nlines;
+        r = g_nccl.Broadcast(J + 8 * o0 * m.nfreqs, J + 8 * o0 * m.nfreqs, nJ, ncclFloat64, root, comm, ctx->stream);
+        if (!r) r = g_nccl.Broadcast(lv + 8 * o0 * m.nlines, lv + 8 * o0 * m.nlines, nL, ncclFloat64, root, comm, ctx->stream);
+        if (!r) r = g_nccl.Broadcast(lc + 4 * o0 * m.nlines, lc + 4 * o0 * m.nlines, nL, ncclUint32, root, comm, ctx->stream);
+    }
     const ncclResult_t r2 = g_nccl.GroupEnd();
-    if (r || r2) return ctx->fail(MGB_ENCCL, "ncclAllGather: %s", g_nccl.GetErrorString(r ? r : r2));
+    if (r || r2) return ctx->fail(MGB_ENCCL, "ncclBroadcast (all-gather of origin slices): %s", g_nccl.GetErrorString(r ? r : r2));
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->res_o0 = 0; ctx->res_o1 = m.npoints;
     return MGB_OK;

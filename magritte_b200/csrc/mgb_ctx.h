@@ -83,6 +83,7 @@ struct mgb_ctx {
     // NCCL
     void* comm = nullptr;
     int nranks = 1, rank = 0;
+    std::vector<uint32_t> part_bounds; // [nranks+1] origin range of every rank (set by mgb_partition / mgb_partition_balanced)
 
     ~mgb_ctx();
     int fail(int code, const char* fmt, ...) {

@@ -30,7 +30,7 @@ def main():
         uid = [ctx.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(world, rank, uid[0])
-        rng = ctx.partition(world, rank)
+        rng = ctx.partition(world, rank, balanced=True)
         if rng[1] > rng[0]:
             ctx.run(approx, rng)
         ctx.allgather()
