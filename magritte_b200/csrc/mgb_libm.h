@@ -59,6 +59,11 @@ MGB_LIBM_TAB uint64_t mgb_exp2f_tab[32] = {
     0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
     0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull};
 
+// expf used inside erff: device code may route it to a shared out-of-line instance (mgb_device.cuh)
+#ifndef MGB_ERFF_EXPF
+#define MGB_ERFF_EXPF mgb_expf
+#endif
+
 // ---- __logf_data / __powf_log2_data share invc; logc is ln(c) resp. log2(c)
 MGB_LIBM_TAB double mgb_log_invc[16] = {
     0x1.661ec79f8f3bep+0, 0x1.571ed4aaf883dp+0, 0x1.49539f0f010b0p+0, 0x1.3c995b0b80385p+0,
@@ -334,7 +339,7 @@ MGB_LIBM_FN float mgb_erff(float x) {
         S = one + s * (sb1 + s * (sb2 + s * (sb3 + s * (sb4 + s * (sb5 + s * (sb6 + s * sb7))))));
     }
     z = MGB_I2F(ix & (int32_t)0xfffff000);
-    r = mgb_expf(-z * z - 0.5625f) * mgb_expf((z - x) * (z + x) + R / S);
+    r = MGB_ERFF_EXPF(-z * z - 0.5625f) * MGB_ERFF_EXPF((z - x) * (z + x) + R / S);
     if (hx >= 0) return one - r / x;
     return r / x - one;
 }

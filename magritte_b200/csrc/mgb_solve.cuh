@@ -132,7 +132,7 @@ __device__ __noinline__ void line_integrated_own(double min_opacity, double line
         const double posY = (linefreq - freqY) * avg_iw;
         const double posX = (linefreq - freqX) * avg_iw;
         const double diff_pos = posY - posX;
-        const float erfdiff   = mgb_erff((float)posY) - mgb_erff((float)posX); /* float subtraction */
+        const float erfdiff   = erff_ool((float)posY) - erff_ool((float)posX); /* float subtraction */
         const double erfterm  = ddiv(avg_op, diff_pos) / 2.0 * (double)erfdiff;
         ld = dz * (avg_iw * erfterm + min_opacity);
     }
@@ -150,6 +150,7 @@ struct SweepState {
     double SatY_far;     // line-integrated source of that segment at its near end (= at X)
     double F, FI, a;     // Rybicki-Hummer F (FF or GG), 1/(1+F), eliminated source (Su)
     bool haveX, X_is_end, large_far;
+    unsigned nlarge;     // segments of this side that took the line-integrated branch
 };
 
 // One entry of the sweep: evaluate eta, chi, S at the record Y = q[0] (get_eta_and_chi_interpolated, then S = eta/chi,
@@ -216,7 +217,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
                 double d = 0.0;
                 const double bound_min_dtau = m.min_opacity * dzX;
                 if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-                dtau = d; S_atX = ddiv(0.0, d); S_atY = S_atX;
+                dtau = d; S_atX = (d > 0.0 && d < CUDART_INF) ? 0.0 : 0.0 / d; S_atY = S_atX; /* (0 + 0) / d */
             } else {
                 const uint2 pX = *reinterpret_cast<const uint2*>(&MGB_REC(x, R_PTS)), pY = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
                 const double fX = MGB_REC(x, R_FACTOR), fY = MGB_REC(q, R_FACTOR);
@@ -259,6 +260,92 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
         st.X_is_end = true;
     }
     st.chiX = chiY; st.SX = SY;
+}
+
+// Out-of-line instance of the general step (boundary rows, windows with other lines, ApproximationType None): taken by a
+// small minority of the entries, kept out of the instruction stream of the common case.
+template <int APPROX>
+__device__ __noinline__ SweepState sweep_step_general(const DevModel& m, LaneLine L, SweepState st, int side, const double* q, uint32_t ll,
+                                                      double freq) {
+    sweep_step<APPROX>(m, L, st, side, q, ll, freq, st.nlarge);
+    return st;
+}
+
+// The common case of sweep_step, arithmetic unchanged: an interior row whose windows (at Y, and over the segment when the
+// shift is large) hold exactly the own line or no line at all. `part` = this lane has an entry in this iteration.
+// Returns false (nothing done) when some participating lane of the warp needs the general step.
+template <int APPROX>
+__device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneLine& L, SweepState& st, int side, const double* q, double freq,
+                                                  bool part) {
+    if (APPROX == APPROX_NONE) return false;
+    const double* x  = q - 1;
+    const double shY = MGB_REC(q, R_SHIFT), shX = MGB_REC(x, R_SHIFT);
+    const double frY = freq * shY;
+    int clsY;
+    if (APPROX == APPROX_CLOSELINES) {
+        const double ub = m.max_dist * (frY * MGB_REC(q, R_SQW));
+        clsY = window_class(L, frY - ub, frY + ub);
+    } else {
+        clsY = L.own ? WIN_OWN : WIN_OTHER;
+    }
+    const double dshift_abs = fabs(shY - shX);
+    const double dX = MGB_REC(x, R_DSM), dY = MGB_REC(q, R_DSM);
+    const double dshift_max = (dY < dX) ? dY : dX;
+    const bool large = dshift_abs > dshift_max;
+    const double frX = freq * shX;
+    int clsS = WIN_OWN;
+    if (APPROX == APPROX_CLOSELINES) {
+        const double left_freq = (frX < frY) ? frX : frY, right_freq = (frX < frY) ? frY : frX;
+        const double bX = m.max_dist * (right_freq * MGB_REC(x, R_SQW));
+        const double bY = m.max_dist * (right_freq * MGB_REC(q, R_SQW));
+        const double ub = (bX < bY) ? bY : bX;
+        clsS = window_class(L, left_freq - ub, right_freq + ub);
+    } else {
+        clsS = clsY;
+    }
+    const bool ok = !part || (st.haveX & !st.X_is_end & (clsY != WIN_OTHER) & (!large | (clsS != WIN_OTHER)));
+    if (!__all_sync(0xffffffffu, ok)) return false;
+    if (!part) return true;
+    const double dzX = MGB_REC(x, R_DZ);
+    double chiY, SY;
+    if (clsY == WIN_OWN) {
+        const double prof = gaussian(MGB_REC(q, R_IW), frY - L.s_own);
+        const double eta  = 0.0 + prof * MGB_REC(q, R_IE);
+        if (APPROX == APPROX_ONELINE) chiY = (0.0 + prof * MGB_REC(q, R_IO)) + m.min_opacity;
+        else chiY = m.min_opacity + prof * MGB_REC(q, R_IO);
+        SY = ddiv(eta, chiY);
+    } else {
+        chiY = m.min_opacity;
+        SY   = (chiY > 0.0 && chiY < CUDART_INF) ? 0.0 : 0.0 / chiY;
+    }
+    double dtau, S_atX = 0.0, S_atY = 0.0;
+    if (large) {
+        st.nlarge++;
+        if (clsS == WIN_OWN) {
+            line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW), MGB_REC(x, R_IO),
+                                        MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE), dtau, S_atX, S_atY);
+        } else {
+            double d = 0.0;
+            const double bound_min_dtau = m.min_opacity * dzX;
+            if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
+            dtau = d; S_atX = (d > 0.0 && d < CUDART_INF) ? 0.0 : 0.0 / d; S_atY = S_atX; /* (0 + 0) / d */
+        }
+    } else {
+        dtau = 0.5 * (st.chiX + chiY) * dzX;
+    }
+    const double Sx      = side ? (st.large_far ? st.SatY_far : st.SX) : (large ? S_atX : st.SX);
+    const double avg     = 0.5 * (st.dtau_far + dtau);
+    const double invFar  = avg * st.dtau_far;
+    const double invNear = avg * dtau;
+    const double Afar    = ddiv(1.0, invFar);
+    st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
+    st.FI = ddiv(1.0, 1.0 + st.F);
+    st.a  = (Afar * st.a + Sx) * st.FI * invNear;
+    st.dtau_far  = dtau;
+    st.large_far = large;
+    st.SatY_far  = S_atY;
+    st.chiX = chiY; st.SX = SY;
+    return true;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -487,7 +574,7 @@ __global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevMod
         const unsigned long long off = __ldg(&pv.poff[hr]);
         const double shift0 = __ldg(&pv.shift0[hr]);
         SweepState st;
-        st.haveX = false; st.X_is_end = false; st.large_far = false;
+        st.haveX = false; st.X_is_end = false; st.large_far = false; st.nlarge = 0;
         st.chiX = st.SX = st.F = st.FI = st.a = st.dtau_far = st.SatY_far = 0.0;
         __syncwarp();
         if (lane < ch.nl) { *ws.isub(lane) = 0; *ws.last(lane) = 0; }
@@ -504,13 +591,19 @@ __global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevMod
             for (uint32_t s = 0; s < S; s++) {
                 const uint32_t e0 = eo[s], ns = eo[s + 1] - e0;
                 const uint32_t nmax = __reduce_max_sync(0xffffffffu, ns);
-                for (uint32_t it = 0; it < nmax; it++)
-                    if (it < ns) sweep_step<APPROX>(m, L, st, side, rb + e0 + it, ll, freq, nlarge);
+                for (uint32_t it = 0; it < nmax; it++) {
+                    const bool part = it < ns;
+                    const double* q = rb + e0 + (part ? it : 0u);
+                    if (!sweep_step_common<APPROX>(m, L, st, side, q, freq, part)) {
+                        if (part) st = sweep_step_general<APPROX>(m, L, st, side, q, ll, freq);
+                    }
+                }
             }
             __syncwarp();
             if (centre) break;
         }
         SC = st.SX; /* source function at the origin */
+        nlarge += st.nlarge;
         if (side == 0) {
             double* s0 = ws.side0(lane);
             s0[0] = st.F; s0[32] = st.FI; s0[64] = st.a; s0[96] = st.dtau_far; s0[128] = st.SatY_far; s0[160] = st.large_far ? 1.0 : 0.0;
