@@ -77,7 +77,7 @@ __global__ void k_libm(int fn, unsigned long long n, const float* x, const float
 
 __global__ void k_ddiv(unsigned long long n, const double* a, const double* b, double* out) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = ddiv(a[i], b[i]);
+    if (i < n) out[i] = (a[i] == 1.0 && !signbit(a[i])) ? drcp(b[i]) : ddiv(a[i], b[i]); /* 1/b call sites use drcp */
 }
 
 // 8 independent DFMA chains per thread; explicit fma() because the file is compiled with -fmad=false.

@@ -118,10 +118,11 @@ __device__ __forceinline__ int window_class(const LaneLine& L, double left, doub
 // dtau is bit-symmetric under exchanging the two ends (differences and the float erf difference negate exactly,
 // sums and min/max commute), so the roles are fixed here and the caller maps S_atX / S_atY onto the reference's
 // Scurr / Snext according to the side. Out of line: it holds two inlined erff and is taken by a minority of segments.
+struct LineIntegral { double dtau, S_atX, S_atY; }; /* returned by value: results stay in registers across the call */
 template <int APPROX>
-__device__ __noinline__ void line_integrated_own(double min_opacity, double linefreq, double freqX, double freqY, double dz, double iwX,
-                                                 double iwY, double ioX, double ioY, double slX, double slY, double& dtau,
-                                                 double& S_atX, double& S_atY) {
+__device__ __noinline__ LineIntegral line_integrated_own(double min_opacity, double linefreq, double freqX, double freqY, double dz, double iwX,
+                                                         double iwY, double ioX, double ioY, double slX, double slY) {
+    double dtau, S_atX, S_atY;
     const double avg_iw = (iwX + iwY) / 2.0;
     const double avg_op = (ioX + ioY) / 2.0;
     double ld;
@@ -136,12 +137,13 @@ __device__ __noinline__ void line_integrated_own(double min_opacity, double line
         const double erfterm  = ddiv(avg_op, diff_pos) / 2.0 * (double)erfdiff;
         ld = dz * (avg_iw * erfterm + min_opacity);
     }
-    if (APPROX == APPROX_ONELINE) { dtau = ld; S_atX = slX; S_atY = slY; return; }
+    if (APPROX == APPROX_ONELINE) { dtau = ld; S_atX = slX; S_atY = slY; return LineIntegral{dtau, S_atX, S_atY}; }
     const double sum_dtau = 0.0 + ld, sum_x = 0.0 + ld * slX, sum_y = 0.0 + ld * slY;
     double d = sum_dtau;
     const double bound_min_dtau = min_opacity * dz;
     if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
     dtau = d; S_atX = ddiv(sum_x, d); S_atY = ddiv(sum_y, d);
+    return LineIntegral{dtau, S_atX, S_atY};
 }
 
 struct SweepState {
@@ -210,8 +212,9 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
                 cls = L.own ? WIN_OWN : WIN_OTHER;
             }
             if (cls == WIN_OWN) {
-                line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW), MGB_REC(x, R_IO),
-                                            MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE), dtau, S_atX, S_atY);
+                const LineIntegral li = line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW),
+                                                                    MGB_REC(x, R_IO), MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE));
+                dtau = li.dtau; S_atX = li.S_atX; S_atY = li.S_atY;
             } else if (cls == WIN_EMPTY) {
                 /* no line in reach: sums stay 0, dtau is bounded below by min_opacity*dz (solver.tpp:2095-2110) */
                 double d = 0.0;
@@ -230,7 +233,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
         if (st.X_is_end) {
             // boundary row (solver.tpp:2240-2262 for `first`, 2283-2297 mirrored for `last`)
             const double S0  = large ? S_atX : st.SX;
-            const double inv = ddiv(1.0, dtau);
+            const double inv = drcp(dtau);
             const double Cb  = 2.0 * inv * inv;
             const double Bm  = 1.0 + 2.0 * inv;
             const double B   = Bm + Cb;
@@ -238,7 +241,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             const double Ib  = boundary_intensity(m, pX.x, freq * shX);
             st.a  = ddiv(S0 + 2.0 * Ib * inv, B);
             st.F  = 0.5 * Bm * dtau * dtau;
-            st.FI = ddiv(1.0, 1.0 + st.F);
+            st.FI = drcp(1.0 + st.F);
         } else {
             // interior row (solver.tpp:2264-2281; mirrored 2306-2311): the row's source is the line-integrated one of the
             // segment in which X is `curr` (the near segment on side 0, the far one on side 1)
@@ -246,9 +249,9 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             const double avg     = 0.5 * (st.dtau_far + dtau);
             const double invFar  = avg * st.dtau_far;
             const double invNear = avg * dtau;
-            const double Afar    = ddiv(1.0, invFar);
+            const double Afar    = drcp(invFar);
             st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-            st.FI = ddiv(1.0, 1.0 + st.F);
+            st.FI = drcp(1.0 + st.F);
             st.a  = (Afar * st.a + Sx) * st.FI * invNear;
         }
         st.dtau_far  = dtau;
@@ -322,8 +325,9 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     if (large) {
         st.nlarge++;
         if (clsS == WIN_OWN) {
-            line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW), MGB_REC(x, R_IO),
-                                        MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE), dtau, S_atX, S_atY);
+            const LineIntegral li = line_integrated_own<APPROX>(m.min_opacity, L.s_own, frX, frY, dzX, MGB_REC(x, R_IW), MGB_REC(q, R_IW),
+                                                                MGB_REC(x, R_IO), MGB_REC(q, R_IO), MGB_REC(x, R_SLINE), MGB_REC(q, R_SLINE));
+            dtau = li.dtau; S_atX = li.S_atX; S_atY = li.S_atY;
         } else {
             double d = 0.0;
             const double bound_min_dtau = m.min_opacity * dzX;
@@ -337,9 +341,9 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const double avg     = 0.5 * (st.dtau_far + dtau);
     const double invFar  = avg * st.dtau_far;
     const double invNear = avg * dtau;
-    const double Afar    = ddiv(1.0, invFar);
+    const double Afar    = drcp(invFar);
     st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-    st.FI = ddiv(1.0, 1.0 + st.F);
+    st.FI = drcp(1.0 + st.F);
     st.a  = (Afar * st.a + Sx) * st.FI * invNear;
     st.dtau_far  = dtau;
     st.large_far = large;
@@ -512,7 +516,7 @@ __device__ __forceinline__ void produce_centre(const DevModel& m, const WarpSmem
 
 // ---------------------------------------------------------------------------------------------------
 template <int APPROX>
-__global__ void __launch_bounds__(128, 3) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
+__global__ void __launch_bounds__(128, 4) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
                                                   const FreqChunk* __restrict__ chunks, uint32_t nchunks_f, uint32_t lpw) {
     const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;

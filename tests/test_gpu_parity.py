@@ -159,8 +159,12 @@ def test_ddiv_matches_ieee_division(ctx):
     special = np.array([0.0, -0.0, 1.0, -1.0, np.inf, -np.inf, np.nan, 5e-324, 2.2250738585072014e-308, 1.7976931348623157e308,
                         1e-310, 3.0, 1e300, 1e-300])
     a4, b4 = [x.ravel() for x in np.meshgrid(special, special)]
-    A = np.concatenate([a, a2, a3, a4, np.ones(1000), rng.integers(1, 1 << 20, 1000).astype(np.float64)])
-    B = np.concatenate([b, b2, b3, b4, rng.uniform(1, 2, 1000), rng.integers(1, 1 << 20, 1000).astype(np.float64)])
+    # reciprocals (a == 1.0 is served by drcp, the unscaled Newton sequence): whole exponent range, typical magnitudes, specials
+    nr = 1 << 22
+    b5 = np.concatenate([(sign(nr) | expo(nr, 0, 2047) | mant(nr)).view(np.float64), np.exp(rng.uniform(-140, 140, nr)), special,
+                         np.ldexp(1.0 + rng.integers(0, 4, 4096) * 2.0 ** -52, rng.integers(-1022, 1024, 4096))])
+    A = np.concatenate([a, a2, a3, a4, np.ones(1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), np.ones(b5.size)])
+    B = np.concatenate([b, b2, b3, b4, rng.uniform(1, 2, 1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), b5])
     got = ctx.ddiv(A, B)
     with np.errstate(all="ignore"):
         want = A / B
