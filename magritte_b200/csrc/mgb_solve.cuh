@@ -181,7 +181,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             SY = ddiv(eta, chiY);
         } else if (cls == WIN_EMPTY) {
             chiY = m.min_opacity;
-            SY   = (chiY > 0.0 && chiY < CUDART_INF) ? 0.0 : 0.0 / chiY; /* eta = 0 */
+            SY   = zero_over(chiY); /* eta = 0 */
         } else {
             const uint2 pp = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
             double eta;
@@ -220,7 +220,7 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
                 double d = 0.0;
                 const double bound_min_dtau = m.min_opacity * dzX;
                 if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-                dtau = d; S_atX = (d > 0.0 && d < CUDART_INF) ? 0.0 : 0.0 / d; S_atY = S_atX; /* (0 + 0) / d */
+                dtau = d; S_atX = zero_over(d); S_atY = S_atX; /* (0 + 0) / d */
             } else {
                 const uint2 pX = *reinterpret_cast<const uint2*>(&MGB_REC(x, R_PTS)), pY = *reinterpret_cast<const uint2*>(&MGB_REC(q, R_PTS));
                 const double fX = MGB_REC(x, R_FACTOR), fY = MGB_REC(q, R_FACTOR);
@@ -297,13 +297,13 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const bool large = dshift_abs > dshift_max;
     const double frX = freq * shX;
     int clsS = WIN_OWN;
-    if (APPROX == APPROX_CLOSELINES) {
+    if (APPROX == APPROX_CLOSELINES && __any_sync(0xffffffffu, large)) { /* the segment's window matters to large shifts only */
         const double left_freq = (frX < frY) ? frX : frY, right_freq = (frX < frY) ? frY : frX;
         const double bX = m.max_dist * (right_freq * MGB_REC(x, R_SQW));
         const double bY = m.max_dist * (right_freq * MGB_REC(q, R_SQW));
         const double ub = (bX < bY) ? bY : bX;
         clsS = window_class(L, left_freq - ub, right_freq + ub);
-    } else {
+    } else if (APPROX != APPROX_CLOSELINES) {
         clsS = clsY;
     }
     const bool ok = !part || (st.haveX & !st.X_is_end & (clsY != WIN_OTHER) & (!large | (clsS != WIN_OTHER)));
@@ -319,7 +319,7 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
         SY = ddiv(eta, chiY);
     } else {
         chiY = m.min_opacity;
-        SY   = (chiY > 0.0 && chiY < CUDART_INF) ? 0.0 : 0.0 / chiY;
+        SY   = zero_over(chiY);
     }
     double dtau, S_atX = 0.0, S_atY = 0.0;
     if (large) {
@@ -332,7 +332,7 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
             double d = 0.0;
             const double bound_min_dtau = m.min_opacity * dzX;
             if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-            dtau = d; S_atX = (d > 0.0 && d < CUDART_INF) ? 0.0 : 0.0 / d; S_atY = S_atX; /* (0 + 0) / d */
+            dtau = d; S_atX = zero_over(d); S_atY = S_atX; /* (0 + 0) / d */
         }
     } else {
         dtau = 0.5 * (st.chiX + chiY) * dzX;
