@@ -341,9 +341,9 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const double avg     = 0.5 * (st.dtau_far + dtau);
     const double invFar  = avg * st.dtau_far;
     const double invNear = avg * dtau;
-    const double Afar    = drcp(invFar);
+    const double Afar    = drcp_inl(invFar);
     st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-    st.FI = drcp(1.0 + st.F);
+    st.FI = drcp_inl(1.0 + st.F);
     st.a  = (Afar * st.a + Sx) * st.FI * invNear;
     st.dtau_far  = dtau;
     st.large_far = large;
