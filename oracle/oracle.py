@@ -125,3 +125,19 @@ class Oracle:
         rc = self.lib.orc_solve(C.byref(m), C.c_uint32(o0), C.c_uint32(o1), C.c_uint32(r0), C.c_uint32(r1), C.c_uint32(hl))
         assert rc == 0
         return self.J
+
+    def image(self, ray_dir, nx, ny, dimension):
+        """The new imager (Solver::image_feautrier_order_2_new_imager) on the model's current frequency discretisation.
+        ray_dir is normed here like Model::compute_image_new does (model.cpp:1014). -> dict(ImX, ImY, I, start_pt, n_tot)."""
+        m = self.m
+        r = np.asarray(ray_dir, dtype=np.float64)
+        r = np.ascontiguousarray(r * (1 / np.sqrt(r[0] * r[0] + r[1] * r[1] + r[2] * r[2])))
+        npix = nx * ny
+        ImX, ImY, I = np.zeros(npix), np.zeros(npix), np.zeros((npix, m.nfreqs))
+        sp, nt = np.zeros(npix, np.uint32), np.zeros(npix, np.uint32)
+        if self.threads:
+            os.environ["OMP_NUM_THREADS"] = str(self.threads)
+        rc = self.lib.orc_image(C.byref(m), C.c_int(dimension), _ptr(r, _f64p), C.c_uint32(nx), C.c_uint32(ny), _ptr(ImX, _f64p),
+                                _ptr(ImY, _f64p), _ptr(I, _f64p), _ptr(sp, _u32p), _ptr(nt, _u32p))
+        assert rc == 0
+        return dict(ImX=ImX, ImY=ImY, I=I, start_pt=sp, n_tot=nt)

@@ -34,3 +34,14 @@ def test_twosided_reordering_error(name):
     assert util.relerr(o.L_val[:, :, 0], ref["ref_lambda_val"]) < 1e-12
     if "ref_u" in ref:
         assert util.relerr(o.u, ref["ref_u"]) < 1e-12
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_oracle_image_bit_exact(name):
+    """The oracle's restatement of the new imager against Image.ImX / ImY / I of the compiled reference: bit for bit."""
+    flat, img = util.load_golden_image(name)
+    o = orc.Oracle(flat, store_u=False)
+    for d, (X, Y, I) in zip(img["directions"], img["images"]):
+        r = o.image(d, img["nx"], img["ny"], img["dimension"])
+        assert np.array_equal(r["ImX"], X) and np.array_equal(r["ImY"], Y)
+        assert np.array_equal(r["I"], I), f"{name} {d}: max rel err {util.relerr(r['I'], I)}"

@@ -101,3 +101,19 @@ def assert_trace_equal(got, want, ctx=""):
         assert np.array_equal(got[k], want[k]), f"{ctx}: {k} differs"
     for k in ("interp_factor", "shift", "dZ"):
         assert np.array_equal(np.asarray(got[k]).view(np.uint64), np.asarray(want[k]).view(np.uint64)), f"{ctx}: {k} not bit-identical"
+
+
+def load_golden_image(name):
+    """-> (flat inputs with the image frequency discretisation, dict(dimension, nx, ny, directions, images=[(ImX, ImY, I)]))
+    from tests/golden/image_<name>.npz (tests/golden/make_golden_image.py; the model is the one of case_<name>.npz)."""
+    flat, _ = load_golden(name)
+    z = np.load(os.path.join(GOLDEN, f"image_{name}.npz"))
+    nu = np.ascontiguousarray(z["nu"])
+    flat["nfreqs"] = int(nu.size)
+    flat["nu"] = np.ascontiguousarray(np.broadcast_to(nu, (flat["npoints"], nu.size)))
+    flat["nu_image"] = nu
+    flat["corresponding_line"] = np.zeros(nu.size, dtype=np.uint32)
+    dirs = z["directions"]
+    img = dict(dimension=int(z["dimension"]), nx=int(z["nx"]), ny=int(z["ny"]), directions=dirs,
+               images=[(z[f"ImX_{i}"], z[f"ImY_{i}"], z[f"I_{i}"]) for i in range(len(dirs))])
+    return flat, img
