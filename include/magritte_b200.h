@@ -139,6 +139,33 @@ int mgb_invalidate_paths(mgb_ctx* ctx);
 int mgb_timer_start(mgb_ctx* ctx);
 int mgb_timer_stop(mgb_ctx* ctx, float* ms);
 
+/* ---- the new imager ------------------------------------------------------ */
+/* Work and timing counters of the last mgb_image_feautrier_order_2. */
+typedef struct mgb_image_stats {
+    uint64_t n_pixels;       /* pixels of this call's range */
+    uint64_t n_entries;      /* ray entries (sub-steps included) summed over the pixels, start points excluded */
+    uint64_t n_solves;       /* pixels x frequencies */
+    uint32_t max_ray_length; /* longest pixel ray (entries): Solver::get_ray_lengths_max_new_imager */
+    uint32_t start_bdy;      /* Geometry::get_closest_bdy_point_in_custom_raydir */
+    uint32_t n_chunks, n_launches;
+    float ms_trace, ms_solve, ms_total;
+    uint32_t reserved;
+} mgb_image_stats;
+/* Model::compute_image_new(rx, ry, rz, Nxpix, Nypix) (model.cpp:999-1035) -> Solver::image_feautrier_order_2_new_imager<approx>
+ * (solver.tpp:576-627): Image::set_coordinates_projection_surface (image.cpp:221-368), per pixel the start search
+ * (trace_ray_imaging_get_start, solver.tpp:808-825), the Rest-frame imaging trace with all-lines sub-stepping
+ * (trace_ray_imaging :840-897, set_data :1003-1043) and image_feautrier_order_2 (:2462-2574) for every frequency.
+ * ray_dir need not be normed (it is normed like model.cpp:1014). dimension = Parameters::dimension() (1 or 3).
+ * Frequencies: nu [nfreqs] when nu_per_point == 0 (Model::compute_spectral_discretisation(nu_min, nu_max, n) gives every
+ * point the same bins, model.cpp:257-300), else nu [npoints][nfreqs] (radiation.frequencies.nu; the pixel uses the row of
+ * its start point, solver.tpp:611-614). Pixels [pix_begin, pix_end) of the nx*ny image (index y + ny*x) are computed.
+ * Outputs (host): ImX, ImY [nx*ny] (may be NULL), I [(pix_end-pix_begin)][nfreqs]. Needs geometry, thermodynamics, lines and
+ * line state; errors mirror the reference's exceptions: zero direction, OneLine (not supported for imaging), and a 1D
+ * model imaged along anything but (0,1,0) (image.cpp:80-86) return MGB_EINVAL / MGB_EUNSUPPORTED with the same text. */
+int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                                uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
+                                double* ImX, double* ImY, double* I, mgb_image_stats* stats);
+
 /* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
 /* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */
 int mgb_nccl_unique_id(void* id128);

@@ -18,7 +18,7 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
-    "mgb_allgather_results", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
+    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
 ]
 
 
@@ -37,6 +37,15 @@ class Stats(C.Structure):
                 ("ms_trace_count", C.c_float), ("ms_trace_fill", C.c_float), ("ms_solve", C.c_float),
                 ("ms_reduce", C.c_float), ("ms_total", C.c_float), ("n_solve_launches", C.c_uint32),
                 ("reserved", C.c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
+
+
+class ImageStats(C.Structure):
+    _fields_ = [("n_pixels", C.c_uint64), ("n_entries", C.c_uint64), ("n_solves", C.c_uint64), ("max_ray_length", C.c_uint32),
+                ("start_bdy", C.c_uint32), ("n_chunks", C.c_uint32), ("n_launches", C.c_uint32), ("ms_trace", C.c_float),
+                ("ms_solve", C.c_float), ("ms_total", C.c_float), ("reserved", C.c_uint32)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved"}
@@ -113,8 +122,9 @@ class Context:
             setattr(self.params, k, v)
         self._check(self.lib.mgb_set_params(self._ctx, C.byref(self.params)), "mgb_set_params")
 
-    def set_model(self, flat):
-        """Upload everything from a `flatten.flatten_model` dict."""
+    def set_model(self, flat, frequencies=True):
+        """Upload everything from a `flatten.flatten_model` dict. frequencies=False skips the line discretisation (an imaging
+        model whose frequencies are passed to image() instead)."""
         f = flat
         self.npoints, self.nlines, self.nfreqs = int(f["npoints"]), int(f["nlines"]), int(f["nfreqs"])
         self.hnrays, self.nrays = int(f["hnrays"]), int(f["nrays"])
@@ -147,9 +157,10 @@ class Context:
         qw, pqw = _p(f["quad_weights"], np.float64)
         self._check(self.lib.mgb_set_lines(self._ctx, C.c_uint32(int(f["nlspecs"])), pnrad, pim, pln, pA,
                                            C.c_uint32(int(f["nquads"])), pqw), "mgb_set_lines")
-        nu, pnu = _p(f["nu"], np.float64)
-        cl, pcl = _p(f["corresponding_line"], np.uint32)
-        self._check(self.lib.mgb_set_frequencies(self._ctx, C.c_uint32(self.nfreqs), pnu, pcl), "mgb_set_frequencies")
+        if frequencies:
+            nu, pnu = _p(f["nu"], np.float64)
+            cl, pcl = _p(f["corresponding_line"], np.uint32)
+            self._check(self.lib.mgb_set_frequencies(self._ctx, C.c_uint32(self.nfreqs), pnu, pcl), "mgb_set_frequencies")
         self.set_line_state(f["emissivity"], f["opacity"], f["inverse_width"], f["population_tot"])
 
     def set_line_state(self, emissivity, opacity, inverse_width, population_tot):
@@ -160,6 +171,21 @@ class Context:
         self._check(self.lib.mgb_set_line_state(self._ctx, pe, po, pw, pt), "mgb_set_line_state")
 
     # ---- run --------------------------------------------------------------------------------
+    def image(self, approx, dimension, ray_dir, nx, ny, nu, pix_range=None):
+        """mgb_image_feautrier_order_2: nu is [nfreqs] (common bins) or [npoints][nfreqs]. -> (ImX, ImY, I[pixels][nfreqs], stats)"""
+        nu, pnu = _p(nu, np.float64)
+        per_point = 1 if nu.ndim == 2 else 0
+        nfreqs = nu.shape[-1]
+        d, pd = _p(ray_dir, np.float64)
+        p0, p1 = pix_range or (0, nx * ny)
+        X, Y, I = np.empty(nx * ny), np.empty(nx * ny), np.empty((p1 - p0, nfreqs))
+        st = ImageStats()
+        self._check(self.lib.mgb_image_feautrier_order_2(self._ctx, C.c_int(approx), C.c_int(dimension), pd, C.c_uint32(nx), C.c_uint32(ny),
+                                                         C.c_uint32(nfreqs), pnu, C.c_int(per_point), C.c_uint64(p0), C.c_uint64(p1),
+                                                         X.ctypes.data_as(C.c_void_p), Y.ctypes.data_as(C.c_void_p),
+                                                         I.ctypes.data_as(C.c_void_p), C.byref(st)), "mgb_image_feautrier_order_2")
+        return X, Y, I, st
+
     def run(self, approx=2, o_range=None):
         o0, o1 = o_range or (0, self.npoints)
         st = Stats()

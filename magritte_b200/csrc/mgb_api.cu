@@ -131,6 +131,27 @@ extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* po
     MGB_TRY(upload(ctx, ctx->bcond, boundary_condition, sizeof(int32_t) * nboundary));
     MGB_TRY(upload(ctx, ctx->btemp, boundary_temperature, sizeof(double) * nboundary));
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); /* host vectors go out of scope */
+    {   /* what the imager's projection surface needs on the host (image.cpp:221-368, points.cpp:22-42, geometry.tpp:346-364) */
+        ctx->h_b2p.assign(nboundary, 0);
+        ctx->h_bpos.assign((size_t)nboundary * 3, 0.0);
+        double mn[3] = {DBL_MAX, DBL_MAX, DBL_MAX}, mx[3] = {DBL_MIN, DBL_MIN, DBL_MIN}; /* numeric_limits<Real>::min() as in the reference */
+        for (uint32_t i = 0; i < npoints; i++) {
+            for (int k = 0; k < 3; k++) {
+                const double v = position[3 * i + k];
+                if (v < mn[k]) mn[k] = v;
+                if (v > mx[k]) mx[k] = v;
+            }
+            const uint32_t b = point2boundary[i];
+            if (b < nboundary) {
+                ctx->h_b2p[b] = i;
+                for (int k = 0; k < 3; k++) ctx->h_bpos[(size_t)b * 3 + k] = position[3 * i + k];
+            }
+        }
+        for (int k = 0; k < 3; k++) ctx->h_center[k] = (mn[k] + mx[k]) / 2;
+        ctx->h_p2b0 = point2boundary[0];
+        for (int k = 0; k < 3; k++) ctx->h_pos_last[k] = position[3 * (size_t)(npoints - 1) + k];
+        if (ctx->h_p2b0 < npoints) for (int k = 0; k < 3; k++) ctx->h_pos_p2b0[k] = position[3 * (size_t)ctx->h_p2b0 + k];
+    }
     DevModel& m = ctx->m;
     m.npoints = npoints; m.nrays = nrays; m.hnrays = nrays / 2; m.nboundary = nboundary; m.spherical = spherical_symmetry ? 1 : 0;
     m.pos = ctx->pos.as<double4>(); m.vel = ctx->vel.as<double4>(); m.csr = ctx->csr.as<uint2>(); m.nbs = ctx->nbs.as<uint32_t>();
@@ -387,6 +408,9 @@ cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc
 }
 
 } // namespace
+
+// shared with mgb_image.cu: per-point derived tables (sqrtw_max, Model::set_dshift_max) up to date
+int mgb_internal_refresh_points(mgb_ctx* ctx) { return refresh_points(ctx); }
 
 // Contiguous origin ranges of equal predicted cost: cost(o) = sum over rays of the geometric ray length (the count pass), plus one
 // entry per ray for the origin itself. Every rank computes the same bounds from the same replicated geometry.

@@ -80,6 +80,15 @@ struct mgb_ctx {
     bool plan_cached = false;
     mgb::PathChunk work;    // reusable chunk when paths are not cached
     mgb::DevBuf scratch_u, scratch_L, counters, origin_tot, cub_tmp;
+    // imager: host copies of what Image::set_coordinates_projection_surface reads (boundary points in boundary order,
+    // Points::center, point2boundary[0])
+    std::vector<double> h_bpos;      // [nboundary][3]
+    std::vector<uint32_t> h_b2p;     // [nboundary]
+    double h_center[3] = {0, 0, 0};
+    uint32_t h_p2b0 = 0;
+    double h_pos_p2b0[3] = {0, 0, 0}; // position[point2boundary[0]] when that is a valid point index
+    double h_pos_last[3] = {0, 0, 0}; // position[npoints-1] (start point of a spherically symmetric image)
+    mgb::DevBuf im_X, im_Y, im_len, im_start, im_shift0, im_poff, im_nr, im_nri, im_fac, im_sh, im_dz, im_I, im_nu;
     // NCCL
     void* comm = nullptr;
     int nranks = 1, rank = 0;
@@ -101,6 +110,8 @@ struct mgb_ctx {
         plan_cached = false;
     }
 };
+
+int mgb_internal_refresh_points(mgb_ctx* ctx); // mgb_api.cu
 
 #define MGB_CUDA(ctx, call)                                                                                         \
     do {                                                                                                            \

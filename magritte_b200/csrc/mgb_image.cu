@@ -1,0 +1,499 @@
+// mgb_image.cu -- the new imager: Solver::image_feautrier_order_2_new_imager<approx> (reference solver.tpp:576-627).
+//
+//   host      Image::set_coordinates_projection_surface (image.cpp:221-368), Geometry::get_closest_bdy_point_in_custom_raydir
+//             (geometry.tpp:346-364): a loop over the boundary points, done once per call on the host copies kept by mgb_set_geometry
+//   k_image_trace<FILL>   one warp per pixel: pixel -> 3D origin (image.cpp:370-398), walk over boundary neighbours to the boundary
+//             point closest to the ray (trace_ray_imaging_get_start, solver.tpp:808-825), Rest-frame imaging trace with the
+//             all-lines sub-stepping of set_data (trace_ray_imaging :840-897, set_data :1003-1043, InterpHelper::get_n_interp).
+//             FILL = false counts the entries, FILL = true writes them (nr, nr_interp, interp_factor, shift, dZ) at the pixel's offset.
+//   k_image_solve<APPROX> one warp per (pixel, 32 frequency bins), lanes = bins: image_feautrier_order_2 (:2462-2574), i.e. the
+//             reference's forward elimination from the far end of the ray to the start point, in the reference's own operation
+//             order (no re-ordering here: Image.I is bit-identical to the CPU reference).
+// Frequencies of an image are not tied to the lines (compute_spectral_discretisation(nu_min, nu_max, n)), so eta/chi use the
+// generic window search of mgb_device.cuh (eta_chi_interp / S_dtau_line_integrated), exactly the reference's loops.
+#include <algorithm>
+#include <cmath>
+
+#include <cub/device/device_scan.cuh>
+
+#include "mgb_ctx.h"
+
+using namespace mgb;
+
+namespace {
+
+struct ImageGeom {
+    double ray[3];    // normed direction
+    double scp[3];    // Image::surface_center_point
+    double center[3]; // Points::center
+    uint32_t start_bdy;
+};
+
+struct ImagePaths { // entries of every pixel of a chunk, in emission order (array index centre-1-e of the reference's scratch)
+    const unsigned long long* poff; // [npix] exclusive prefix of len
+    uint32_t* nr;
+    uint32_t* nri;
+    double* fac;
+    double* sh;
+    double* dz;
+};
+
+// image.cpp:370-398
+__device__ __forceinline__ void surface_coords_to_3D(const ImageGeom& g, double x, double y, double& ox, double& oy, double& oz) {
+    const double rx = g.ray[0], ry = g.ray[1], rz = g.ray[2];
+    const double denominator = sqrt(rx * rx + ry * ry);
+    const double inverse_denominator = 1.0 / denominator;
+    const double ix = ry * inverse_denominator, iy = -rx * inverse_denominator;
+    const double jx = rx * rz * inverse_denominator, jy = ry * rz * inverse_denominator, jz = -denominator;
+    if (denominator >= 1.0e-9) {
+        ox = (x * ix + y * jx) + g.scp[0]; oy = (x * iy + y * jy) + g.scp[1]; oz = (y * jz) + g.scp[2];
+    } else {
+        ox = x + g.scp[0]; oy = y + g.scp[1]; oz = 0.0 + g.scp[2];
+    }
+}
+
+// Geometry::get_boundary_point_closer_to_custom_ray (geometry.tpp:310-338): lanes scan the neighbour list; the winner is the
+// first boundary neighbour (list order) with the smallest distance strictly below the current point's.
+__device__ __forceinline__ uint32_t warp_bdy_closer(const DevModel& m, const RayFrame& fr, uint32_t crt, unsigned lane) {
+    const double4 Pc = ldg4(&m.pos[crt]);
+    const double Rcx = Pc.x - fr.ox, Rcy = Pc.y - fr.oy, Rcz = Pc.z - fr.oz;
+    const double Zc  = dot3(Rcx, Rcy, Rcz, fr.dx, fr.dy, fr.dz);
+    const double d0  = dot3(Rcx, Rcy, Rcz, Rcx, Rcy, Rcz) - Zc * Zc;
+    const uint2 c = __ldg(&m.csr[crt]);
+    double best = d0;
+    uint32_t besti = 0xffffffffu, bestn = crt;
+    for (uint32_t i = lane; i < c.y; i += 32) {
+        const uint32_t n = __ldg(&m.nbs[c.x + i]);
+        if (__ldg(&m.p2b[n]) != m.npoints) {
+            const double4 P = ldg4(&m.pos[n]);
+            const double Rx = P.x - fr.ox, Ry = P.y - fr.oy, Rz = P.z - fr.oz;
+            const double Zn = dot3(Rx, Ry, Rz, fr.dx, fr.dy, fr.dz);
+            const double d2 = dot3(Rx, Ry, Rz, Rx, Ry, Rz) - Zn * Zn;
+            if (d2 < best) { best = d2; besti = i; bestn = n; }
+        }
+    }
+    double mn = best;
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+        const double o = __shfl_xor_sync(0xffffffffu, mn, off);
+        mn = (o < mn) ? o : mn;
+    }
+    const uint32_t key = (besti != 0xffffffffu && best == mn) ? besti : 0xffffffffu;
+    const uint32_t win = __reduce_min_sync(0xffffffffu, key);
+    if (win == 0xffffffffu) return crt;
+    return __shfl_sync(0xffffffffu, bestn, (int)(win & 31u));
+}
+
+// Geometry::get_distance_origin_to_boundary (geometry.tpp:167-191)
+__device__ __forceinline__ double distance_origin_to_boundary(const DevModel& m, const RayFrame& fr, uint32_t bdy) {
+    const double4 P = ldg4(&m.pos[bdy]);
+    double Z = dot3(fr.dx, fr.dy, fr.dz, P.x - fr.ox, P.y - fr.oy, P.z - fr.oz);
+    if (m.spherical) {
+        const double Rcos  = dot3(fr.ox, fr.oy, fr.oz, fr.dx, fr.dy, fr.dz);
+        const double R2    = dot3(fr.ox, fr.oy, fr.oz, fr.ox, fr.oy, fr.oz);
+        const double Rsin2 = R2 - Rcos * Rcos;
+        const double horz_dist2 = dot3(P.x, P.y, P.z, P.x, P.y, P.z) - Rsin2;
+        if (horz_dist2 > 0) Z = -sqrt(horz_dist2) - Rcos; else Z = -Rcos;
+    }
+    return Z;
+}
+
+// get_shift<Rest>(origin, 0, raydir, c, Z, false) (geometry.tpp:218-221, 408-418, 452-465)
+__device__ __forceinline__ double get_shift_rest(const DevModel& m, const RayFrame& fr, uint32_t c, double Z) {
+    const double4 vc = ldg4(&m.vel[c]);
+    if (m.spherical) {
+        const double px = ldg4(&m.pos[c]).x;
+        if (px == 0.0) return 1.0;
+        const double Rcos_plus_Z = dot3(fr.ox, fr.oy, fr.oz, fr.dx, fr.dy, fr.dz) + Z;
+        return 1.0 + vc.x * Rcos_plus_Z / px;
+    }
+    return 1.0 + dot3(vc.x, vc.y, vc.z, fr.dx, fr.dy, fr.dz);
+}
+
+// InterpHelper::get_n_interp (solver_interp_helper.tpp:10-46): the largest |logf(crit_next / crit_curr)| over ALL lines
+// (lanes stride the lines; std::max_element keeps the largest value, NaNs are never selected unless first).
+__device__ __forceinline__ uint32_t warp_n_interp_all(const DevModel& m, uint32_t curr, uint32_t next, unsigned lane) {
+    float mx = -1.0f; /* |.| >= 0 */
+    for (uint32_t l = lane; l < m.nlines; l += 32) {
+        const double x = __ldg(&m.lrow[(size_t)next * m.nlines + l].criterion);
+        const double y = __ldg(&m.lrow[(size_t)curr * m.nlines + l].criterion);
+        const float d  = fabsf(mgb_logf((float)(x / y)));
+        if (mx < d) mx = d;
+    }
+#pragma unroll
+    for (int off = 16; off; off >>= 1) {
+        const float o = __shfl_xor_sync(0xffffffffu, mx, off);
+        mx = (mx < o) ? o : mx;
+    }
+    const uint32_t n = to_size(ceil((double)mx / m.log_max_interp_diff));
+    return n > 1 ? n : 1;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Tracer: one warp per pixel. reference: solver.tpp:591-607 (driver part), 808-825, 840-897, 1003-1043
+// ---------------------------------------------------------------------------------------------------
+template <bool FILL>
+__global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, unsigned long long pix0, uint32_t npix,
+                                                     const double* __restrict__ ImX, const double* __restrict__ ImY,
+                                                     uint32_t* __restrict__ len, uint32_t* __restrict__ start, double* __restrict__ shift0,
+                                                     ImagePaths ip, unsigned long long* __restrict__ counters) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t w      = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= npix) return;
+    if (FILL && len[w] == 0) return;
+    RayFrame fr;
+    surface_coords_to_3D(g, ImX[pix0 + w], ImY[pix0 + w], fr.ox, fr.oy, fr.oz);
+    fr.dx = g.ray[0]; fr.dy = g.ray[1]; fr.dz = g.ray[2];
+    fr.vx = fr.vy = fr.vz = 0.0;
+    // trace_ray_imaging_get_start
+    uint32_t c = g.start_bdy;
+    for (;;) {
+        const uint32_t nx = warp_bdy_closer(m, fr, c, lane);
+        if (nx == c) break;
+        c = nx;
+    }
+    double Z = distance_origin_to_boundary(m, fr, c);
+    const double sh0 = get_shift_rest(m, fr, c, Z);
+    // trace_ray_imaging
+    unsigned long long off = FILL ? ip.poff[w] : 0ull;
+    uint32_t n = 0, ns;
+    bool accessed_non_boundary = false;
+    double dZ = 0.0;
+    uint32_t crt = c;
+    uint32_t nxt = warp_get_next(m, fr, c, Z, dZ, ns, lane);
+    if (nxt < m.npoints) {
+        double shift_crt = get_shift_rest(m, fr, crt, Z - dZ);
+        double shift_nxt = get_shift_rest(m, fr, nxt, Z);
+        for (;;) {
+            // set_data (solver.tpp:1003-1043)
+            const uint32_t ni = warp_n_interp_all(m, crt, nxt, lane);
+            if (FILL) {
+                if (ni > 1) {
+                    const double dZ_interpl     = dZ / ni;
+                    const double dshift_interpl = (shift_nxt - shift_crt) / ni;
+                    for (uint32_t i = 1 + lane; i <= ni; i += 32) {
+                        const unsigned long long e = off + n + (i - 1);
+                        ip.nr[e] = nxt; ip.nri[e] = crt;
+                        ip.sh[e]  = shift_crt + i * dshift_interpl;
+                        ip.fac[e] = 1.0 - ((double)i) / ni;
+                        ip.dz[e]  = dZ_interpl;
+                    }
+                } else if (lane == 0) {
+                    const unsigned long long e = off + n;
+                    ip.nr[e] = nxt; ip.nri[e] = crt; ip.sh[e] = shift_nxt; ip.fac[e] = 0.0; ip.dz[e] = dZ;
+                }
+            }
+            n += ni;
+            const double4 P = ldg4(&m.pos[nxt]);
+            const bool interior = __ldg(&m.p2b[nxt]) == m.npoints;
+            if (!(interior || dot3(P.x - g.center[0], P.y - g.center[1], P.z - g.center[2], fr.dx, fr.dy, fr.dz) < 0)) break;
+            crt = nxt; shift_crt = shift_nxt;
+            if (interior) accessed_non_boundary = true;
+            nxt = warp_get_next(m, fr, crt, Z, dZ, ns, lane);
+            if (!(nxt < m.npoints)) break;
+            shift_nxt = get_shift_rest(m, fr, nxt, Z);
+        }
+    }
+    if (!FILL && lane == 0) {
+        // a ray that only touched boundary points is dropped in general geometry (solver.tpp:892-896): n_tot = 1
+        const uint32_t L = (accessed_non_boundary || m.spherical) ? n : 0u;
+        len[w] = L; start[w] = c; shift0[w] = sh0;
+        atomicAdd(&counters[0], (unsigned long long)L);
+        atomicMax((unsigned int*)&counters[1], n); /* get_ray_lengths_max_new_imager counts every walk */
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Solve: one warp per (pixel, 32 frequency bins); lanes = bins. reference: solver.tpp:2139-2186 (compute_source_dtau),
+// 2462-2574 (image_feautrier_order_2), 609-621 (Image.I)
+// ---------------------------------------------------------------------------------------------------
+template <int APPROX>
+__device__ __forceinline__ void image_source_dtau(const DevModel& m, const Entry& c, const Entry& n, double curr_freq, double next_freq,
+                                                  double dz, bool& compute_curr_opacity, double& dtau_n, double& chi_c, double& chi_n,
+                                                  double& S_c, double& S_n) {
+    const double dshift_abs = fabs(n.shift - c.shift);
+    const double a = __ldg(&m.dshift_max[c.p1]), b = __ldg(&m.dshift_max[n.p1]);
+    const double dshift_max = (b < a) ? b : a; /* std::min(a, b) */
+    if (dshift_abs > dshift_max) {
+        compute_curr_opacity = true;
+        S_dtau_line_integrated<APPROX>(m, c, n, 0u, curr_freq, next_freq, dz, dtau_n, S_c, S_n);
+    } else {
+        if (compute_curr_opacity) {
+            compute_curr_opacity = false;
+            double eta_c;
+            eta_chi_interp<APPROX>(m, c, 0u, curr_freq, eta_c, chi_c);
+            S_c = ddiv(eta_c, chi_c);
+        }
+        double eta_n;
+        eta_chi_interp<APPROX>(m, n, 0u, next_freq, eta_n, chi_n);
+        S_n    = ddiv(eta_n, chi_n);
+        dtau_n = 0.5 * (chi_c + chi_n) * dz;
+    }
+}
+
+template <int APPROX>
+__global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, uint32_t nfreqs, uint32_t nchunks_f,
+                                                     const double* __restrict__ nu, uint32_t nu_stride,
+                                                     const uint32_t* __restrict__ len, const uint32_t* __restrict__ start,
+                                                     const double* __restrict__ shift0, ImagePaths ip, double* __restrict__ I) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (item >= (size_t)npix * nchunks_f) return;
+    const uint32_t pix = (uint32_t)(item / nchunks_f), cf = (uint32_t)(item % nchunks_f);
+    const uint32_t f0  = cf * 32 + lane;
+    const bool active  = f0 < nfreqs;
+    const uint32_t f   = active ? f0 : nfreqs - 1;
+    const uint32_t c   = start[pix];
+    const uint32_t L   = len[pix];
+    const double freq  = __ldg(&nu[(size_t)c * nu_stride + f]);
+    double out;
+    if (L == 0) {
+        out = boundary_intensity(m, c, freq); /* n_tot = 1 (solver.tpp:616-620) */
+    } else {
+        const unsigned long long off = ip.poff[pix];
+        Entry cur, nxt;
+        cur.p1 = ip.nr[off + L - 1]; cur.p2 = ip.nri[off + L - 1]; cur.factor = ip.fac[off + L - 1]; cur.shift = ip.sh[off + L - 1];
+        bool compute_curr_opacity = true;
+        double chi_c = 0.0, chi_n = 0.0, term_c = 0.0, term_n = 0.0, dtau_n = 0.0, dtau_c;
+        double Su = 0.0, FF = 0.0, FI = 0.0;
+        for (uint32_t e = L; e-- > 0;) {
+            if (e > 0) {
+                nxt.p1 = ip.nr[off + e - 1]; nxt.p2 = ip.nri[off + e - 1]; nxt.factor = ip.fac[off + e - 1]; nxt.shift = ip.sh[off + e - 1];
+            } else { /* the start point: nr_[centre], shift_[centre]; nr_interp_/interp_factor_ stay value-initialised (0) */
+                nxt.p1 = c; nxt.p2 = 0u; nxt.factor = 0.0; nxt.shift = shift0[pix];
+            }
+            const double dz = ip.dz[off + e];
+            if (e == L - 1) {
+                image_source_dtau<APPROX>(m, cur, nxt, freq * cur.shift, freq * nxt.shift, dz, compute_curr_opacity, dtau_n, chi_c, chi_n,
+                                          term_c, term_n);
+                const double inverse_dtau_f = drcp(dtau_n);
+                const double Cf        = 2.0 * inverse_dtau_f * inverse_dtau_f;
+                const double Bf_min_Cf = 1.0 + 2.0 * inverse_dtau_f;
+                const double Bf        = Bf_min_Cf + Cf;
+                const double I_bdy_f   = boundary_intensity(m, cur.p1, freq * cur.shift);
+                Su = term_c + 2.0 * I_bdy_f * inverse_dtau_f;
+                Su = ddiv(Su, Bf);
+                FF = 0.5 * Bf_min_Cf * dtau_n * dtau_n;
+                FI = drcp(1.0 + FF);
+            } else {
+                term_c = term_n; dtau_c = dtau_n; chi_c = chi_n;
+                image_source_dtau<APPROX>(m, cur, nxt, freq * cur.shift, freq * nxt.shift, dz, compute_curr_opacity, dtau_n, chi_c, chi_n,
+                                          term_c, term_n);
+                const double dtau_avg  = 0.5 * (dtau_c + dtau_n);
+                const double inverse_A = dtau_avg * dtau_c;
+                const double inverse_C = dtau_avg * dtau_n;
+                const double A         = drcp(inverse_A);
+                const double FFn       = (A * FF * FI + 1.0) * inverse_C;
+                const double FIn       = drcp(1.0 + FFn);
+                Su = (A * Su + term_c) * FIn * inverse_C;
+                FF = FFn; FI = FIn;
+            }
+            cur = nxt;
+        }
+        const double inverse_dtau_l = drcp(dtau_n);
+        const double Al          = 2.0 * inverse_dtau_l * inverse_dtau_l;
+        const double Bl_min_Al   = 1.0 + 2.0 * inverse_dtau_l;
+        const double Bl          = Bl_min_Al + Al;
+        const double denominator = drcp(Bl * FF + Bl_min_Al);
+        const double I_bdy_l     = boundary_intensity(m, cur.p1, freq * cur.shift);
+        double Sl = term_n + 2.0 * I_bdy_l * inverse_dtau_l;
+        Sl = (Al * Su + Sl) * (1.0 + FF) * denominator;
+        out = 2.0 * Sl - boundary_intensity(m, cur.p1, freq);
+    }
+    if (active) I[(size_t)pix * nfreqs + f] = out;
+}
+
+} // namespace
+
+namespace {
+struct Stopwatch {
+    cudaEvent_t a = nullptr, b = nullptr;
+    cudaStream_t s;
+    explicit Stopwatch(cudaStream_t st) : s(st) { cudaEventCreate(&a); cudaEventCreate(&b); }
+    ~Stopwatch() { if (a) cudaEventDestroy(a); if (b) cudaEventDestroy(b); }
+    void start() { cudaEventRecord(a, s); }
+    float stop() { cudaEventRecord(b, s); cudaEventSynchronize(b); float ms = 0.f; cudaEventElapsedTime(&ms, a, b); return ms; }
+};
+
+// Image::set_coordinates_projection_surface (image.cpp:221-368) on the host copies of the boundary points.
+void projection_surface(const mgb_ctx* ctx, int dimension, ImageGeom& g, uint32_t nx, uint32_t ny, std::vector<double>& ImX,
+                        std::vector<double>& ImY) {
+    const uint32_t nb = (uint32_t)ctx->h_b2p.size();
+    const double* bp  = ctx->h_bpos.data();
+    double max_x = -DBL_MAX, max_y = -DBL_MAX, min_x = DBL_MAX, min_y = DBL_MAX;
+    if (dimension == 1) {
+        for (uint32_t b = 0; b < nb; b++) { max_x = std::max(max_x, bp[3 * b]); min_x = std::min(min_x, bp[3 * b]); }
+        max_x = std::max(std::abs(min_x), max_x);
+        min_x = -max_x; min_y = min_x; max_y = max_x;
+    }
+    if (dimension == 3) {
+        const double rx = g.ray[0], ry = g.ray[1], rz = g.ray[2];
+        const double denominator = sqrt(rx * rx + ry * ry);
+        const double inverse_denominator = 1.0 / denominator;
+        const double ix = ry * inverse_denominator, iy = -rx * inverse_denominator;
+        const double jx = rx * rz * inverse_denominator, jy = ry * rz * inverse_denominator, jz = -denominator;
+        for (uint32_t b = 0; b < nb; b++) {
+            const double* P = bp + 3 * (size_t)b;
+            double X, Y;
+            if (denominator >= 1.0e-9) { X = ix * P[0] + iy * P[1]; Y = jx * P[0] + jy * P[1] + jz * P[2]; }
+            else { X = P[0]; Y = P[1]; }
+            min_x = std::min(min_x, X); max_x = std::max(max_x, X); min_y = std::min(min_y, Y); max_y = std::max(max_y, Y);
+        }
+    }
+    // Geometry::get_closest_bdy_point_in_custom_raydir (geometry.tpp:346-364). The reference's first guess is
+    // boundary.point2boundary[0] used as a POINT index (sic); when point 0 is interior that is npoints and the reference reads one
+    // element past the position array: such a first guess is dropped here. Boundary index 0 is never examined, as in the reference.
+    const DevModel& m = ctx->m;
+    double cp[3] = {0, 0, 0};
+    if (m.spherical) {
+        g.start_bdy = m.npoints - 1;
+        for (int k = 0; k < 3; k++) cp[k] = ctx->h_pos_last[k];
+    } else {
+        uint32_t closest = ctx->h_p2b0;
+        double dmin = HUGE_VAL;
+        if (closest < m.npoints) {
+            for (int k = 0; k < 3; k++) cp[k] = ctx->h_pos_p2b0[k];
+            dmin = g.ray[0] * cp[0] + g.ray[1] * cp[1] + g.ray[2] * cp[2];
+        }
+        for (uint32_t b = 1; b < nb; b++) {
+            const double* P = bp + 3 * (size_t)b;
+            const double d  = g.ray[0] * P[0] + g.ray[1] * P[1] + g.ray[2] * P[2];
+            if (d < dmin) { closest = ctx->h_b2p[b]; dmin = d; for (int k = 0; k < 3; k++) cp[k] = P[k]; }
+        }
+        g.start_bdy = closest;
+    }
+    double distance_from_origin = cp[0] * g.ray[0] + cp[1] * g.ray[1] + cp[2] * g.ray[2];
+    if (m.spherical) distance_from_origin = -cp[0];
+    for (int k = 0; k < 3; k++) g.scp[k] = g.ray[k] * distance_from_origin;
+    const double deltax = (max_x - min_x) / (nx), deltay = (max_y - min_y) / (ny);
+    ImX.resize((size_t)nx * ny); ImY.resize((size_t)nx * ny);
+    for (uint32_t xi = 0; xi < nx; xi++) {
+        const double xloc = min_x + deltax / 2.0 + xi * deltax;
+        for (uint32_t yi = 0; yi < ny; yi++) {
+            ImX[yi + (size_t)ny * xi] = xloc;
+            ImY[yi + (size_t)ny * xi] = min_y + deltay / 2.0 + yi * deltay;
+        }
+    }
+}
+} // namespace
+
+#define MGB_TRY_(x) do { int rc_ = (x); if (rc_ != MGB_OK) return rc_; } while (0)
+
+extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                                           uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
+                                           double* ImX_out, double* ImY_out, double* I_out, mgb_image_stats* stats) {
+    if (!ctx) return MGB_EINVAL;
+    if (!(ctx->have_geometry && ctx->have_thermo && ctx->have_lines && ctx->have_state))
+        return ctx->fail(MGB_ESTATE, "mgb_image_feautrier_order_2: model incomplete (geometry %d thermo %d lines %d state %d)",
+                         ctx->have_geometry, ctx->have_thermo, ctx->have_lines, ctx->have_state);
+    if (!ray_dir || !nu || !I_out || !nx || !ny || !nfreqs) return ctx->fail(MGB_EINVAL, "mgb_image_feautrier_order_2: null or zero argument");
+    const uint64_t npix_all = (uint64_t)nx * ny;
+    if (pix_begin >= pix_end || pix_end > npix_all) return ctx->fail(MGB_EINVAL, "pixel range [%llu,%llu) invalid for %llu pixels",
+                                                                     (unsigned long long)pix_begin, (unsigned long long)pix_end, (unsigned long long)npix_all);
+    if (pix_end - pix_begin > 0xffffffffull) return ctx->fail(MGB_EINVAL, "more than 2^32 pixels in one call");
+    // Model::compute_image_new (model.cpp:1008-1035)
+    const double n2 = ray_dir[0] * ray_dir[0] + ray_dir[1] * ray_dir[1] + ray_dir[2] * ray_dir[2];
+    if (n2 == 0.0) return ctx->fail(MGB_EINVAL, "The given ray direction vector does not point in a direction. Please use a non-zero (normed) "
+                                                "direction vector to generate an image.");
+    if (approx == APPROX_ONELINE) return ctx->fail(MGB_EUNSUPPORTED, "One line approximation is not supported for imaging.");
+    if (approx != APPROX_NONE && approx != APPROX_CLOSELINES) return ctx->fail(MGB_EINVAL, "approx must be 0 (None) or 2 (CloseLines)");
+    if (dimension != 1 && dimension != 3) return ctx->fail(MGB_EINVAL, "dimension must be 1 or 3 (Image::set_coordinates_projection_surface)");
+    ImageGeom g;
+    const double inv_norm = 1 / std::sqrt(n2);
+    for (int k = 0; k < 3; k++) g.ray[k] = ray_dir[k] * inv_norm;
+    if (dimension == 1 && (g.ray[0] != 0.0 || g.ray[1] != 1.0 || g.ray[2] != 0.0))
+        return ctx->fail(MGB_EINVAL, "In 1D, the image ray has to be (0,1,0)"); /* image.cpp:80-86 */
+    for (int k = 0; k < 3; k++) g.center[k] = ctx->h_center[k];
+    cudaSetDevice(ctx->device);
+    const DevModel& m = ctx->m;
+    std::vector<double> hX, hY;
+    projection_surface(ctx, dimension, g, nx, ny, hX, hY);
+    if (ImX_out) memcpy(ImX_out, hX.data(), 8 * hX.size());
+    if (ImY_out) memcpy(ImY_out, hY.data(), 8 * hY.size());
+
+    mgb_image_stats st;
+    memset(&st, 0, sizeof st);
+    Stopwatch total(ctx->stream);
+    total.start();
+    MGB_TRY_(mgb_internal_refresh_points(ctx)); /* Model::set_dshift_max (setup_new_imager, solver.tpp:26) and the CloseLines window width */
+    const uint32_t npix = (uint32_t)(pix_end - pix_begin);
+    const size_t nu_elems = nu_per_point ? (size_t)m.npoints * nfreqs : (size_t)nfreqs;
+    MGB_CUDA(ctx, ctx->im_X.ensure(8 * hX.size())); MGB_CUDA(ctx, ctx->im_Y.ensure(8 * hY.size()));
+    MGB_CUDA(ctx, ctx->im_nu.ensure(8 * nu_elems));
+    MGB_CUDA(ctx, cudaMemcpyAsync(ctx->im_X.p, hX.data(), 8 * hX.size(), cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, cudaMemcpyAsync(ctx->im_Y.p, hY.data(), 8 * hY.size(), cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, cudaMemcpyAsync(ctx->im_nu.p, nu, 8 * nu_elems, cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, ctx->im_len.ensure(4 * (size_t)npix)); MGB_CUDA(ctx, ctx->im_start.ensure(4 * (size_t)npix));
+    MGB_CUDA(ctx, ctx->im_shift0.ensure(8 * (size_t)npix)); MGB_CUDA(ctx, ctx->im_poff.ensure(8 * (size_t)npix));
+    MGB_CUDA(ctx, ctx->counters.ensure(64));
+    MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+    // ---- count pass over the whole pixel range ----
+    Stopwatch tt(ctx->stream);
+    tt.start();
+    ImagePaths none{};
+    k_image_trace<false><<<(unsigned)(((size_t)npix * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+        m, g, pix_begin, npix, ctx->im_X.as<double>(), ctx->im_Y.as<double>(), ctx->im_len.as<uint32_t>(), ctx->im_start.as<uint32_t>(),
+        ctx->im_shift0.as<double>(), none, ctx->counters.as<unsigned long long>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    st.n_launches++;
+    st.ms_trace += tt.stop();
+    std::vector<uint32_t> hlen(npix);
+    unsigned long long cnt[2];
+    MGB_CUDA(ctx, cudaMemcpy(hlen.data(), ctx->im_len.p, 4 * (size_t)npix, cudaMemcpyDeviceToHost));
+    MGB_CUDA(ctx, cudaMemcpy(cnt, ctx->counters.p, 16, cudaMemcpyDeviceToHost));
+    st.n_entries = cnt[0]; st.max_ray_length = (uint32_t)cnt[1];
+    // ---- pixel chunks: bounded entry storage (32 B per entry) and bounded result rows ----
+    const unsigned long long entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / 32ull);
+    const uint32_t pix_budget = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / (8 * (size_t)nfreqs));
+    const uint32_t nchunks_f  = (nfreqs + 31) / 32;
+    for (uint32_t p0 = 0; p0 < npix;) {
+        uint32_t p1 = p0;
+        unsigned long long ents = 0;
+        while (p1 < npix && (p1 - p0) < pix_budget) {
+            if (p1 > p0 && ents + hlen[p1] > entry_budget) break;
+            ents += hlen[p1]; p1++;
+        }
+        const uint32_t np = p1 - p0;
+        const size_t ne   = (size_t)std::max<unsigned long long>(ents, 1);
+        MGB_CUDA(ctx, ctx->im_nr.ensure(4 * ne)); MGB_CUDA(ctx, ctx->im_nri.ensure(4 * ne)); MGB_CUDA(ctx, ctx->im_fac.ensure(8 * ne));
+        MGB_CUDA(ctx, ctx->im_sh.ensure(8 * ne)); MGB_CUDA(ctx, ctx->im_dz.ensure(8 * ne));
+        MGB_CUDA(ctx, ctx->im_I.ensure(8 * (size_t)np * nfreqs));
+        tt.start();
+        const uint32_t* len_c = ctx->im_len.as<uint32_t>() + p0;
+        unsigned long long* poff = ctx->im_poff.as<unsigned long long>() + p0;
+        size_t tmp = 0;
+        cub::DeviceScan::ExclusiveSum(nullptr, tmp, len_c, poff, (int64_t)np, ctx->stream);
+        MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+        MGB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, len_c, poff, (int64_t)np, ctx->stream));
+        ImagePaths ip{poff, ctx->im_nr.as<uint32_t>(), ctx->im_nri.as<uint32_t>(), ctx->im_fac.as<double>(), ctx->im_sh.as<double>(),
+                      ctx->im_dz.as<double>()};
+        k_image_trace<true><<<(unsigned)(((size_t)np * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+            m, g, pix_begin + p0, np, ctx->im_X.as<double>(), ctx->im_Y.as<double>(), ctx->im_len.as<uint32_t>() + p0,
+            ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip, nullptr);
+        MGB_CUDA(ctx, cudaGetLastError());
+        st.n_launches += 2;
+        st.ms_trace += tt.stop();
+        tt.start();
+        const size_t nitems = (size_t)np * nchunks_f;
+        const unsigned blocks = (unsigned)((nitems * 32 + 127) / 128);
+        const uint32_t stride = nu_per_point ? nfreqs : 0u;
+        if (approx == APPROX_NONE)
+            k_image_solve<APPROX_NONE><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,
+                                                                        ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip,
+                                                                        ctx->im_I.as<double>());
+        else
+            k_image_solve<APPROX_CLOSELINES><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,
+                                                                              ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0,
+                                                                              ip, ctx->im_I.as<double>());
+        MGB_CUDA(ctx, cudaGetLastError());
+        st.n_launches++;
+        st.ms_solve += tt.stop();
+        MGB_CUDA(ctx, cudaMemcpy(I_out + (size_t)p0 * nfreqs, ctx->im_I.p, 8 * (size_t)np * nfreqs, cudaMemcpyDeviceToHost));
+        st.n_chunks++;
+        p0 = p1;
+    }
+    st.ms_total = total.stop();
+    st.n_pixels = npix; st.n_solves = (uint64_t)npix * nfreqs; st.start_bdy = g.start_bdy;
+    if (stats) *stats = st;
+    return MGB_OK;
+}
