@@ -1,0 +1,140 @@
+// bindings.cpp -- pybind11 module `magritte_b200.core`: the Python face of mgbh::Model, with the method names of
+// magritte.core.Model for the Feautrier order-2 path (reference src/bindings/pybindings.cpp:123-271). Arrays go in and out
+// as numpy arrays in the reference's layouts. The nested attribute tree of the reference (model.geometry.points.position.set(...))
+// is provided on the Python side by magritte_b200/model.py on top of these setters.
+#include <pybind11/numpy.h>
+#include <pybind11/pybind11.h>
+#include <pybind11/stl.h>
+
+#include "mgb_host.hpp"
+
+namespace py = pybind11;
+using namespace mgbh;
+template <class T> using arr = py::array_t<T, py::array::c_style | py::array::forcecast>;
+
+template <class T> static std::vector<T> vec(const arr<T>& a) { return std::vector<T>(a.data(), a.data() + a.size()); }
+static py::array_t<double> out2(const std::vector<double>& v, size_t r, size_t c) {
+    py::array_t<double> a({r, c});
+    std::copy(v.begin(), v.begin() + r * c, a.mutable_data());
+    return a;
+}
+
+PYBIND11_MODULE(core, m) {
+    m.doc() = "magritte_b200.core: B200 drop-in for the Feautrier order-2 path of magritte.core";
+    m.attr("CC") = CC; m.attr("HH") = HH; m.attr("KB") = KB; m.attr("AMU") = AMU; m.attr("T_CMB") = T_CMB;
+
+    py::class_<Parameters>(m, "Parameters")
+        .def_readwrite("n_off_diag", &Parameters::n_off_diag)
+        .def_readwrite("max_width_fraction", &Parameters::max_width_fraction)
+        .def_readwrite("convergence_fraction", &Parameters::convergence_fraction)
+        .def_readwrite("min_rel_pop_for_convergence", &Parameters::min_rel_pop_for_convergence)
+        .def_readwrite("pop_prec", &Parameters::pop_prec)
+        .def_readwrite("min_opacity", &Parameters::min_opacity)
+        .def_property("min_line_opacity", [](const Parameters& p) { return (double)p.min_line_opacity; }, [](Parameters& p, double v) { p.min_line_opacity = v; })
+        .def_property("min_line_emissivity", [](const Parameters& p) { return (double)p.min_line_emissivity; }, [](Parameters& p, double v) { p.min_line_emissivity = v; })
+        .def_readwrite("max_interpolation_diff", &Parameters::max_interpolation_diff)
+        .def_readwrite("max_distance_opacity_contribution", &Parameters::max_distance_opacity_contribution)
+        .def_readwrite("population_inversion_fraction", &Parameters::population_inversion_fraction)
+        .def_readwrite("use_adaptive_Ng_acceleration", &Parameters::use_adaptive_Ng_acceleration)
+        .def_readwrite("adaptive_Ng_acceleration_use_max_criterion", &Parameters::adaptive_Ng_acceleration_use_max_criterion)
+        .def_readwrite("Ng_acceleration_mem_limit", &Parameters::Ng_acceleration_mem_limit)
+        .def_readwrite("adaptive_Ng_acceleration_min_order", &Parameters::adaptive_Ng_acceleration_min_order)
+        .def_readwrite("Ng_acceleration_remove_N_its", &Parameters::Ng_acceleration_remove_N_its)
+        .def_readwrite("one_line_approximation", &Parameters::one_line_approximation)
+        .def_readwrite("sum_opacity_emissivity_over_all_lines", &Parameters::sum_opacity_emissivity_over_all_lines)
+        .def_readwrite("spherical_symmetry", &Parameters::spherical_symmetry)
+        .def_readwrite("dimension", &Parameters::dimension);
+
+    py::class_<Image>(m, "Image")
+        .def_readonly("nfreqs", &Image::nfreqs)
+        .def_property_readonly("ImX", [](const Image& i) { return py::array_t<double>(i.ImX.size(), i.ImX.data()); })
+        .def_property_readonly("ImY", [](const Image& i) { return py::array_t<double>(i.ImY.size(), i.ImY.data()); })
+        .def_property_readonly("freqs", [](const Image& i) { return py::array_t<double>(i.freqs.size(), i.freqs.data()); })
+        .def_property_readonly("I", [](const Image& i) { return out2(i.I, (size_t)i.nx * i.ny, i.nfreqs); });
+
+    py::class_<Model>(m, "Model")
+        .def(py::init<>())
+        .def_readwrite("device", &Model::device)
+        .def_readonly("parameters", &Model::parameters, py::return_value_policy::reference_internal)
+        .def_readonly("images", &Model::images)
+        .def_readonly("error_mean", &Model::error_mean)
+        .def_readonly("error_max", &Model::error_max)
+        .def_readonly("seconds_radiation_field", &Model::seconds_radiation_field)
+        .def_readonly("seconds_statistical_equilibrium", &Model::seconds_statistical_equilibrium)
+        .def("mutable_parameters", [](Model& s) -> Parameters& { return s.parameters; }, py::return_value_policy::reference_internal)
+        .def("set_geometry", [](Model& s, arr<double> pos, arr<double> vel, arr<uint32_t> nn, arr<uint32_t> nbs, arr<double> dir, arr<double> w,
+                                arr<uint32_t> anti, arr<uint32_t> b2p, arr<int32_t> bc, arr<double> bt) {
+            s.set_geometry((Size)nn.size(), pos.data(), vel.data(), nn.data(), nbs.data(), (size_t)nbs.size(), (Size)w.size(), dir.data(), w.data(),
+                           anti.data(), (Size)b2p.size(), b2p.data(), bc.data(), bt.data());
+        })
+        .def("set_thermodynamics", [](Model& s, arr<double> T, arr<double> v) { s.set_thermodynamics(T.data(), v.data()); })
+        .def("set_abundance", [](Model& s, arr<double> ab) { s.set_abundance(ab.data(), (Size)ab.shape(1)); })
+        .def("add_species", [](Model& s, py::dict d) {
+            LineProducingSpecies ls;
+            Linedata& ld = ls.linedata;
+            ld.num = d["num"].cast<Size>(); ld.nlev = d["nlev"].cast<Size>(); ld.nrad = d["nrad"].cast<Size>();
+            ld.inverse_mass = d["inverse_mass"].cast<double>();
+            ld.irad = vec(d["irad"].cast<arr<uint32_t>>()); ld.jrad = vec(d["jrad"].cast<arr<uint32_t>>());
+            ld.energy = vec(d["energy"].cast<arr<double>>()); ld.weight = vec(d["weight"].cast<arr<double>>());
+            ld.frequency = vec(d["frequency"].cast<arr<double>>()); ld.A = vec(d["A"].cast<arr<double>>());
+            ld.Ba = vec(d["Ba"].cast<arr<double>>()); ld.Bs = vec(d["Bs"].cast<arr<double>>());
+            for (auto h : d["colpar"].cast<py::list>()) {
+                py::dict c = h.cast<py::dict>();
+                CollisionPartner cp;
+                cp.num_col_partner = c["num_col_partner"].cast<Size>(); cp.orth_or_para_H2 = c["orth_or_para_H2"].cast<std::string>();
+                cp.icol = vec(c["icol"].cast<arr<uint32_t>>()); cp.jcol = vec(c["jcol"].cast<arr<uint32_t>>());
+                cp.tmp = vec(c["tmp"].cast<arr<double>>());
+                auto Ce = c["Ce"].cast<arr<double>>(), Cd = c["Cd"].cast<arr<double>>();
+                for (py::ssize_t t = 0; t < Ce.shape(0); t++) {
+                    cp.Ce.emplace_back(Ce.data() + t * Ce.shape(1), Ce.data() + (t + 1) * Ce.shape(1));
+                    cp.Cd.emplace_back(Cd.data() + t * Cd.shape(1), Cd.data() + (t + 1) * Cd.shape(1));
+                }
+                ld.colpar.push_back(std::move(cp));
+            }
+            ls.quadrature_roots = vec(d["quadrature_roots"].cast<arr<double>>());
+            ls.quadrature_weights = vec(d["quadrature_weights"].cast<arr<double>>());
+            s.add_species(std::move(ls));
+        })
+        .def("compute_inverse_line_widths", &Model::compute_inverse_line_widths)
+        .def("compute_spectral_discretisation", py::overload_cast<>(&Model::compute_spectral_discretisation))
+        .def("compute_spectral_discretisation", py::overload_cast<Real, Real>(&Model::compute_spectral_discretisation))
+        .def("compute_spectral_discretisation", py::overload_cast<Real, Real, Size>(&Model::compute_spectral_discretisation))
+        .def("compute_LTE_level_populations", &Model::compute_LTE_level_populations)
+        .def("compute_radiation_field_feautrier_order_2", &Model::compute_radiation_field_feautrier_order_2)
+        .def("compute_Jeff", &Model::compute_Jeff)
+        .def("compute_level_populations_from_stateq", &Model::compute_level_populations_from_stateq)
+        .def("compute_level_populations", &Model::compute_level_populations)
+        .def("compute_image_new", &Model::compute_image_new)
+        // test hook: radiation.J and the diagonal Lambda lists as a radiation-field call leaves them (host-only tests of compute_Jeff / stateq)
+        .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt) {
+            s.J = vec(J);
+            const Size L = s.nlines();
+            for (Size l = 0; l < s.nlspecs(); l++) {
+                auto& ls = s.lineProducingSpecies[l];
+                const Size nrad = ls.linedata.nrad;
+                for (Size p = 0; p < s.npoints; p++)
+                    for (Size k = 0; k < nrad; k++) {
+                        ls.lambda_Ls[(size_t)p * nrad + k]  = lam.data()[(size_t)p * L + s.nrad_cum[l] + k];
+                        ls.lambda_cnt[(size_t)p * nrad + k] = cnt.data()[(size_t)p * L + s.nrad_cum[l] + k];
+                    }
+            }
+        })
+        // results (copies, reference layouts)
+        .def("get_J", [](const Model& s) { return out2(s.J, s.npoints, s.nfreqs); })
+        .def("get_nu", [](const Model& s) { return out2(s.nu, s.npoints, s.nfreqs); })
+        .def("get_emissivity", [](const Model& s) { return out2(s.emissivity, s.npoints, s.nlines()); })
+        .def("get_opacity", [](const Model& s) { return out2(s.opacity, s.npoints, s.nlines()); })
+        .def("get_inverse_width", [](const Model& s) { return out2(s.inverse_width, s.npoints, s.nlines()); })
+        .def("get_population", [](const Model& s, Size l) { /* lineProducingSpecies[l].population, long double -> double */
+            const auto& ls = s.lineProducingSpecies.at(l);
+            py::array_t<double> a({(size_t)s.npoints, (size_t)ls.linedata.nlev});
+            for (size_t i = 0; i < ls.population.size(); i++) a.mutable_data()[i] = (double)ls.population[i];
+            return a;
+        })
+        .def("get_population_tot", [](const Model& s, Size l) { const auto& v = s.lineProducingSpecies.at(l).population_tot; return py::array_t<double>(v.size(), v.data()); })
+        .def("get_Jeff", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.Jeff, s.npoints, ls.linedata.nrad); })
+        .def("get_Jlin", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.Jlin, s.npoints, ls.linedata.nrad); })
+        .def("get_lambda", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.lambda_Ls, s.npoints, ls.linedata.nrad); })
+        .def("convergence", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l);
+                                                         return py::make_tuple(ls.fraction_not_converged, ls.relative_change_mean, ls.relative_change_max); });
+}

@@ -1,0 +1,758 @@
+// mgb_host.hpp -- host side of the drop-in: a C++ `Model` with the method names of magritte.core's Model for the Feautrier
+// order-2 path (reference src/model/model.hpp:19-122, bound in src/bindings/pybindings.cpp:123-271). It owns the host arrays
+// in the reference's layouts and drives the GPU exclusively through the C ABI of include/magritte_b200.h; there is no CPU
+// implementation of the radiation field here (without a CUDA device compute_radiation_field_feautrier_order_2 throws).
+//
+// What is implemented on the host, in the reference's operation order and number types (Real = double, populations in
+// long double like Eigen's VectorXld, lineProducingSpecies.hpp:46):
+//   compute_inverse_line_widths     Lines::set_inverse_width                 lines.tpp:45-59
+//   compute_spectral_discretisation Model::compute_spectral_discretisation   model.cpp:70-161 (lines) and :257-300 (image bins)
+//   compute_LTE_level_populations   Lines::iteration_using_LTE               lines.cpp:82-91, lineProducingSpecies.tpp:49-69
+//   compute_Jeff                    Model::compute_Jeff                      model.cpp:514-545
+//   compute_level_populations_from_stateq / compute_level_populations       model.cpp:655-748, lines.cpp:93-137,
+//                                   lineProducingSpecies.tpp:128-165 (convergence), 266-314 / 316-364 (Ng acceleration),
+//                                   377-581 (statistical equilibrium), 711-802 (negative populations / inversions)
+// The statistical-equilibrium system of the reference is one global sparse LU (Eigen::SparseLU, long double). With the
+// diagonal Lambda operator of this path (n_off_diag = 0) it is block diagonal -- one nlev x nlev block per point -- and is
+// solved here block by block with a dense long-double LU with partial pivoting: same equations, different pivot order.
+#pragma once
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <ctime>
+#include <limits>
+#include <numeric>
+#include <stdexcept>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/magritte_b200.h"
+
+namespace mgbh {
+
+typedef double Real;   // reference tools/types.hpp:25
+typedef uint32_t Size; // reference tools/types.hpp:26
+typedef long double LD;
+
+// reference src/tools/constants.hpp
+constexpr double CC = 2.99792458E+8, HH = 6.62607004E-34, KB = 1.38064852E-23, AMU = 1.66053904E-27, T_CMB = 2.7254800;
+constexpr double CC_SQUARED = 8.98755179E+16;
+constexpr double TWO_KB_OVER_AMU_CC_SQUARED = 2.0 * KB / (AMU * CC_SQUARED);
+const double FOUR_PI = 4.0 * M_PI;
+const double HH_OVER_FOUR_PI = HH / FOUR_PI;
+
+struct Parameters { // reference src/model/parameters/parameters.hpp:66-124 (the tunables this path reads)
+    Size n_off_diag = 0;
+    Real max_width_fraction = 0.35, convergence_fraction = 0.995, min_rel_pop_for_convergence = 1.0e-10, pop_prec = 1.0e-6;
+    Real min_opacity = 1.0e-26;
+    LD min_line_opacity = 1.0e-13, min_line_emissivity = 1.0e-50;
+    Real max_interpolation_diff = 1.4, max_distance_opacity_contribution = 10.0;
+    Real population_inversion_fraction = -1.0;
+    bool store_intensities = false, use_adaptive_Ng_acceleration = true, adaptive_Ng_acceleration_use_max_criterion = true;
+    Size Ng_acceleration_mem_limit = 9, adaptive_Ng_acceleration_min_order = 2, Ng_acceleration_remove_N_its = 0;
+    bool one_line_approximation = false, sum_opacity_emissivity_over_all_lines = false;
+    bool spherical_symmetry = false;
+    Size dimension = 3;
+};
+
+struct CollisionPartner { // reference linedata/collisionPartner/collisionPartner.hpp
+    Size num_col_partner = 0;
+    std::string orth_or_para_H2 = "n";
+    std::vector<Size> icol, jcol;
+    std::vector<Real> tmp;
+    std::vector<std::vector<Real>> Ce, Cd; // [ntmp][ncol]
+    std::vector<Real> Ce_intpld, Cd_intpld;
+
+    // reference src/tools/interpolation.hpp: search()
+    static Size search(const std::vector<Real>& x, const Real value) {
+        Size start = 0, stop = (Size)x.size() - 1;
+        if (value >= x[stop]) return stop;
+        else if (value <= x[start]) return start;
+        while (stop > start + 1) {
+            const Size middle = (stop + start) / 2;
+            if (value > x[middle]) start = middle;
+            else if (value < x[middle]) stop = middle;
+            else return middle;
+        }
+        return stop;
+    }
+    // collisionPartner.tpp: interpolate_collision_coefficients
+    void interpolate_collision_coefficients(const Real temperature_gas) {
+        const Size ntmp = (Size)tmp.size(), ncol = (Size)icol.size();
+        const Size t = search(tmp, temperature_gas);
+        if (t == 0) { Ce_intpld = Ce[0]; Cd_intpld = Cd[0]; }
+        else if (t == ntmp - 1) { Ce_intpld = Ce[ntmp - 1]; Cd_intpld = Cd[ntmp - 1]; }
+        else {
+            const Real step = (temperature_gas - tmp[t - 1]) / (tmp[t] - tmp[t - 1]);
+            Ce_intpld.resize(ncol); Cd_intpld.resize(ncol);
+            for (Size k = 0; k < ncol; k++) {
+                Ce_intpld[k] = Ce[t - 1][k] + (Ce[t][k] - Ce[t - 1][k]) * step;
+                Cd_intpld[k] = Cd[t - 1][k] + (Cd[t][k] - Cd[t - 1][k]) * step;
+            }
+        }
+    }
+    // collisionPartner.tpp: adjust_abundance_for_ortho_or_para
+    void adjust_abundance_for_ortho_or_para(const Real temperature_gas, Real& abundance) const {
+        if (orth_or_para_H2 != "n") {
+            const Real frac_H2_para = 1.0 / (1.0 + 9.0 * expf(-170.5 / temperature_gas));
+            if (orth_or_para_H2 == "o") abundance *= (1.0 - frac_H2_para);
+            if (orth_or_para_H2 == "p") abundance *= frac_H2_para;
+        }
+    }
+};
+
+struct Linedata { // reference linedata/linedata.hpp
+    Size num = 0, nlev = 0, nrad = 0;
+    Real inverse_mass = 0.0;
+    std::vector<Size> irad, jrad;
+    std::vector<Real> energy, weight, frequency, A, Ba, Bs;
+    std::vector<CollisionPartner> colpar;
+};
+
+typedef std::vector<LD> VecLD;
+inline LD dot(const VecLD& a, const VecLD& b) { LD s = 0; for (size_t i = 0; i < a.size(); i++) s += a[i] * b[i]; return s; }
+
+// Dense long-double LU with partial pivoting, in place: A [n][n] row-major, b [n] -> solution. false on a zero pivot.
+inline bool lu_solve(std::vector<LD>& A, std::vector<LD>& b, const Size n) {
+    for (Size c = 0; c < n; c++) {
+        Size piv = c;
+        LD big = fabsl(A[(size_t)c * n + c]);
+        for (Size r = c + 1; r < n; r++) if (fabsl(A[(size_t)r * n + c]) > big) { big = fabsl(A[(size_t)r * n + c]); piv = r; }
+        if (big == 0.0L) return false;
+        if (piv != c) { for (Size k = 0; k < n; k++) std::swap(A[(size_t)c * n + k], A[(size_t)piv * n + k]); std::swap(b[c], b[piv]); }
+        const LD inv = 1.0L / A[(size_t)c * n + c];
+        for (Size r = c + 1; r < n; r++) {
+            const LD f = A[(size_t)r * n + c] * inv;
+            if (f == 0.0L) continue;
+            for (Size k = c + 1; k < n; k++) A[(size_t)r * n + k] -= f * A[(size_t)c * n + k];
+            b[r] -= f * b[c];
+        }
+    }
+    for (Size r = n; r-- > 0;) {
+        LD s = b[r];
+        for (Size k = r + 1; k < n; k++) s -= A[(size_t)r * n + k] * b[k];
+        b[r] = s / A[(size_t)r * n + r];
+    }
+    return true;
+}
+
+// Least-squares / square solve by Householder QR with column pivoting (what RTR.colPivHouseholderQr().solve(ones) does in the
+// reference's Ng acceleration, lineProducingSpecies.tpp:300-302); rank decided with Eigen's default threshold n * epsilon.
+inline VecLD colpiv_qr_solve(std::vector<LD> A, VecLD b, const Size n) {
+    std::vector<Size> perm(n);
+    std::iota(perm.begin(), perm.end(), 0u);
+    std::vector<LD> rdiag(n, 0.0L);
+    Size rank = n;
+    LD maxpivot = 0.0L;
+    for (Size k = 0; k < n; k++) {
+        Size best = k; LD bn = -1.0L;
+        for (Size c = k; c < n; c++) { LD s = 0; for (Size r = k; r < n; r++) s += A[(size_t)r * n + c] * A[(size_t)r * n + c]; if (s > bn) { bn = s; best = c; } }
+        if (best != k) { for (Size r = 0; r < n; r++) std::swap(A[(size_t)r * n + k], A[(size_t)r * n + best]); std::swap(perm[k], perm[best]); }
+        LD norm = sqrtl(bn);
+        if (k == 0) maxpivot = norm;
+        if (norm <= maxpivot * (LD)n * std::numeric_limits<LD>::epsilon()) { rank = k; break; }
+        const LD alpha = (A[(size_t)k * n + k] > 0) ? -norm : norm;
+        std::vector<LD> v(n - k);
+        for (Size r = k; r < n; r++) v[r - k] = A[(size_t)r * n + k];
+        v[0] -= alpha;
+        LD vn = 0; for (LD x : v) vn += x * x;
+        if (vn > 0) {
+            for (Size c = k; c < n; c++) {
+                LD s = 0; for (Size r = k; r < n; r++) s += v[r - k] * A[(size_t)r * n + c];
+                s = 2.0L * s / vn;
+                for (Size r = k; r < n; r++) A[(size_t)r * n + c] -= s * v[r - k];
+            }
+            LD s = 0; for (Size r = k; r < n; r++) s += v[r - k] * b[r];
+            s = 2.0L * s / vn;
+            for (Size r = k; r < n; r++) b[r] -= s * v[r - k];
+        }
+        rdiag[k] = A[(size_t)k * n + k];
+    }
+    VecLD y(n, 0.0L), x(n, 0.0L);
+    for (Size r = rank; r-- > 0;) {
+        LD s = b[r];
+        for (Size c = r + 1; c < rank; c++) s -= A[(size_t)r * n + c] * y[c];
+        y[r] = s / A[(size_t)r * n + r];
+    }
+    for (Size k = 0; k < n; k++) x[perm[k]] = y[k];
+    return x;
+}
+
+struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
+    const Parameters* parameters = nullptr;
+    Size npoints = 0;
+    Linedata linedata;
+    std::vector<Real> quadrature_roots, quadrature_weights;
+    VecLD population, population_prev1, population_prev2, population_prev3, trial_population, trial_population_prev;
+    std::vector<Real> population_tot;
+    std::vector<VecLD> populations, residuals;
+    std::vector<Real> Jlin, Jeff, Jdif;      // [npoints][nrad]
+    std::vector<Real> lambda_Ls;             // [npoints][nrad] the diagonal ALO element (nr == p), lambda.tpp:79-89
+    std::vector<Size> lambda_cnt;            // [npoints][nrad] list length (0 or 1)
+    Real fraction_not_converged = 0, relative_change_mean = 0, relative_change_max = 0;
+
+    Size index(const Size p, const Size i) const { return i + p * linedata.nlev; }
+
+    void resize(const Size np) {
+        npoints = np;
+        const size_t n = (size_t)np * linedata.nlev;
+        population.assign(n, 0); population_prev1.assign(n, 0); population_prev2.assign(n, 0); population_prev3.assign(n, 0);
+        trial_population.assign(n, 0); trial_population_prev.assign(n, 0);
+        population_tot.assign(np, 0);
+        Jlin.assign((size_t)np * linedata.nrad, 0); Jeff = Jlin; Jdif = Jlin; lambda_Ls = Jlin;
+        lambda_cnt.assign((size_t)np * linedata.nrad, 0);
+    }
+    // lineProducingSpecies.tpp:23-44
+    Real get_emissivity(const Size p, const Size k) const {
+        const Size i = index(p, linedata.irad[k]);
+        const Real freq = linedata.frequency[k];
+        return std::max(freq * HH_OVER_FOUR_PI * linedata.A[k] * population[i], parameters->min_line_emissivity);
+    }
+    Real get_opacity(const Size p, const Size k) const {
+        const Size i = index(p, linedata.irad[k]), j = index(p, linedata.jrad[k]);
+        const Real freq = linedata.frequency[k];
+        return std::max(freq * HH_OVER_FOUR_PI * (population[j] * linedata.Ba[k] - population[i] * linedata.Bs[k]), parameters->min_line_opacity);
+    }
+    // lineProducingSpecies.tpp:49-69
+    void update_using_LTE(const std::vector<Real>& abundance, const Size nspecs, const std::vector<Real>& temperature) {
+        for (Size p = 0; p < npoints; p++) {
+            population_tot[p] = abundance[(size_t)p * nspecs + linedata.num];
+            Real partition_function = 0.0;
+            for (Size i = 0; i < linedata.nlev; i++) {
+                const Size ind = index(p, i);
+                population[ind] = linedata.weight[i] * exp(-linedata.energy[i] / (KB * temperature[p]));
+                partition_function += population[ind];
+            }
+            for (Size i = 0; i < linedata.nlev; i++) population[index(p, i)] *= population_tot[p] / partition_function;
+        }
+        populations.push_back(population);
+    }
+    // lineProducingSpecies.tpp:75-92
+    void set_LTE(const std::vector<Real>& temperature, const Size p, const Size k) {
+        const Size i = index(p, linedata.irad[k]), j = index(p, linedata.jrad[k]);
+        Real population_tot_line = population[i] + population[j];
+        Real partition_function  = 0.0;
+        population[i] = linedata.weight[linedata.irad[k]] * exp(-linedata.energy[linedata.irad[k]] / (KB * temperature[p]));
+        population[j] = linedata.weight[linedata.jrad[k]] * exp(-linedata.energy[linedata.jrad[k]] / (KB * temperature[p]));
+        partition_function = population[i] + population[j];
+        population[i] *= population_tot_line / partition_function;
+        population[j] *= population_tot_line / partition_function;
+    }
+    // lineProducingSpecies.tpp:98-121
+    void set_LTE_specific_levels(const std::vector<Real>& temperature, const Size p, const std::vector<char>& level_mask) {
+        Real population_tot_levels = 0.0, partition_function = 0.0;
+        for (Size i = 0; i < linedata.nlev; i++)
+            if (level_mask[i]) {
+                const Size ind = index(p, i);
+                population_tot_levels += population[ind];
+                population[ind] = linedata.weight[i] * exp(-linedata.energy[i] / (KB * temperature[p]));
+                partition_function += population[ind];
+            }
+        for (Size i = 0; i < linedata.nlev; i++)
+            if (level_mask[i]) population[index(p, i)] *= population_tot_levels / partition_function;
+    }
+    // lineProducingSpecies.tpp:128-165 (the reference reduces with OpenMP; the order of that sum is not fixed there either)
+    void check_for_convergence(const Real pop_prec) {
+        const Real weight = 1.0 / (npoints * linedata.nlev);
+        Real fnc = 0.0, rcm = 0.0, rcmax = 0.0;
+        for (Size p = 0; p < npoints; p++)
+            for (Size i = 0; i < linedata.nlev; i++) {
+                const Size ind = index(p, i);
+                if (population[ind] > parameters->min_rel_pop_for_convergence * population_tot[p]) {
+                    const Real relative_change = 2.0 * std::abs((population[ind] - population_prev1[ind]) / (population[ind] + population_prev1[ind]));
+                    if (relative_change > pop_prec) fnc += weight;
+                    rcm += (weight * relative_change);
+                    rcmax = std::max(relative_change, rcmax);
+                }
+            }
+        fraction_not_converged = fnc; relative_change_mean = rcm; relative_change_max = rcmax;
+    }
+    // lineProducingSpecies.tpp:171-201
+    void check_for_convergence_trial(const Real pop_prec) {
+        const Real weight = 1.0 / (npoints * linedata.nlev);
+        Real fnc = 0.0, rcm = 0.0, rcmax = 0.0;
+        for (Size p = 0; p < npoints; p++)
+            for (Size i = 0; i < linedata.nlev; i++) {
+                const Size ind = index(p, i);
+                const Real relative_change = 2.0 * std::abs((trial_population[ind] - trial_population_prev[ind]) / (trial_population[ind] + trial_population_prev[ind]));
+                if (relative_change > pop_prec) fnc += weight;
+                rcm += (weight * relative_change);
+                rcmax = std::max(relative_change, rcmax);
+            }
+        fraction_not_converged = fnc; relative_change_mean = rcm; relative_change_max = rcmax;
+    }
+    VecLD ng_combination(const Size order) const { // the shared core of update_using_acceleration[_trial], :287-309 / :340-361
+        const Size popsize = (Size)populations.size(), ressize = (Size)residuals.size();
+        std::vector<LD> RTR((size_t)order * order);
+        for (Size i = 0; i < order; i++)
+            for (Size j = 0; j < order; j++) RTR[(size_t)i * order + j] = dot(residuals[ressize - order + i], residuals[ressize - order + j]);
+        VecLD coef = colpiv_qr_solve(RTR, VecLD(order, 1.0L), order);
+        LD sum = 0; for (LD c : coef) sum += c;
+        for (LD& c : coef) c /= sum;
+        VecLD out(population.size(), 0.0L);
+        for (Size i = 0; i < order; i++) {
+            const VecLD& P = populations[popsize - 1 - i];
+            const LD c = coef[order - 1 - i];
+            for (size_t n = 0; n < out.size(); n++) out[n] += P[n] * c;
+        }
+        return out;
+    }
+    static VecLD diff(const VecLD& a, const VecLD& b) { VecLD r(a.size()); for (size_t i = 0; i < a.size(); i++) r[i] = a[i] - b[i]; return r; }
+    // lineProducingSpecies.tpp:266-314
+    void update_using_acceleration(const Size order) {
+        population_prev3 = population_prev2; population_prev2 = population_prev1; population_prev1 = population;
+        residuals.push_back(diff(population, populations.back()));
+        populations.push_back(population);
+        if (populations.size() < (residuals.size() + 1)) throw std::runtime_error("Error during ng acceleration; inconstent sizes.");
+        if (residuals.size() < order) throw std::runtime_error("Error during ng acceleration; order of acceleration greather than data stored.");
+        population = ng_combination(order);
+        residuals.clear();
+        populations.erase(populations.begin(), populations.end() - 1);
+    }
+    // lineProducingSpecies.tpp:316-371
+    void update_using_acceleration_trial(const Size order) {
+        residuals.push_back(diff(population, populations.back()));
+        populations.push_back(population);
+        trial_population_prev = trial_population;
+        if (populations.size() < (residuals.size() + 1)) throw std::runtime_error("Error during ng acceleration; inconstent sizes.");
+        if (populations.size() < order) throw std::runtime_error("Error during ng acceleration; order of acceleration greather than data stored.");
+        trial_population = ng_combination(order);
+        residuals.pop_back();
+        populations.pop_back();
+    }
+    // lineProducingSpecies.tpp:377-581, block by block (see the header comment). Needs Jeff and the diagonal Lambda element.
+    void update_using_statistical_equilibrium(const std::vector<Real>& abundance, const Size nspecs, const std::vector<Real>& temperature) {
+        const Size nlev = linedata.nlev;
+        population_prev3 = population_prev2; population_prev2 = population_prev1; population_prev1 = population;
+        residuals.push_back(diff(population, populations.back()));
+        populations.push_back(population);
+        bool failed = false;
+#pragma omp parallel
+        {
+            std::vector<LD> M((size_t)nlev * nlev), y(nlev);
+            std::vector<CollisionPartner> cps = linedata.colpar; /* interpolation buffers are per thread */
+#pragma omp for schedule(static)
+            for (Size p = 0; p < npoints; p++) {
+                std::fill(M.begin(), M.end(), 0.0L);
+                std::fill(y.begin(), y.end(), 0.0L);
+                auto add = [&](Size r, Size c, LD v) { M[(size_t)r * nlev + c] += v; };
+                for (Size k = 0; k < linedata.nrad; k++) {
+                    const LD v_IJ = linedata.A[k] + linedata.Bs[k] * Jeff[(size_t)p * linedata.nrad + k];
+                    const LD v_JI = linedata.Ba[k] * Jeff[(size_t)p * linedata.nrad + k];
+                    const Size I = linedata.irad[k], J = linedata.jrad[k];
+                    if (J != nlev - 1) { add(J, I, +v_IJ); add(J, J, -v_JI); }
+                    if (I != nlev - 1) { add(I, J, +v_JI); add(I, I, -v_IJ); }
+                }
+                for (Size k = 0; k < linedata.nrad; k++)
+                    for (Size m = 0; m < lambda_cnt[(size_t)p * linedata.nrad + k]; m++) { /* nr == p: the diagonal element */
+                        const Real freq = linedata.frequency[k];
+                        const LD v_IJ   = -lambda_Ls[(size_t)p * linedata.nrad + k] * get_opacity(p, k) / freq;
+                        const Size I = linedata.irad[k], J = linedata.jrad[k];
+                        if (J != nlev - 1) add(J, I, +v_IJ);
+                        if (I != nlev - 1) add(I, I, -v_IJ);
+                    }
+                for (CollisionPartner& colpar : cps) {
+                    Real abn = abundance[(size_t)p * nspecs + colpar.num_col_partner];
+                    Real tmp = temperature[p];
+                    colpar.adjust_abundance_for_ortho_or_para(tmp, abn);
+                    colpar.interpolate_collision_coefficients(tmp);
+                    for (Size k = 0; k < colpar.icol.size(); k++) {
+                        const LD v_IJ = colpar.Cd_intpld[k] * abn;
+                        const LD v_JI = colpar.Ce_intpld[k] * abn;
+                        const Size I = colpar.icol[k], J = colpar.jcol[k];
+                        if (J != nlev - 1) { add(J, I, +v_IJ); add(J, J, -v_JI); }
+                        if (I != nlev - 1) { add(I, J, +v_JI); add(I, I, -v_IJ); }
+                    }
+                }
+                for (Size i = 0; i < nlev; i++) add(nlev - 1, i, 1.0L);
+                y[nlev - 1] = population_tot[p];
+                if (!lu_solve(M, y, nlev)) { failed = true; continue; }
+                for (Size i = 0; i < nlev; i++) population[index(p, i)] = y[i];
+            }
+        }
+        if (failed) throw std::runtime_error("Eigen solver ERROR."); /* same text as lineProducingSpecies.tpp:551 */
+    }
+    // lineProducingSpecies.tpp:711-802
+    void correct_negative_populations(const std::vector<Real>& temperature) {
+        const Size nlev = linedata.nlev;
+        for (Size p = 0; p < npoints; p++)
+            if (population_tot[p] > 0.0) {
+                Real total_positive_population = 0.0;
+                for (Size i = 0; i < nlev; i++) {
+                    if (population[p * nlev + i] < 0.0) population[p * nlev + i] = 0.0;
+                    else total_positive_population += population[p * nlev + i];
+                }
+                for (Size i = 0; i < nlev; i++) population[p * nlev + i] = population[p * nlev + i] * population_tot[p] / total_positive_population;
+            }
+        for (Size p = 0; p < npoints; p++) {
+            std::vector<char> modified_level(nlev, false);
+            Size next_n_modified_levels = 0, curr_n_modified_levels = 0;
+            auto inverted = [&](Size k) {
+                const Size i = index(p, linedata.irad[k]), j = index(p, linedata.jrad[k]);
+                return population[j] < linedata.Bs[k] / linedata.Ba[k] * population[i] * parameters->population_inversion_fraction;
+            };
+            do {
+                curr_n_modified_levels = next_n_modified_levels;
+                bool population_inversion_at_point = false;
+                for (Size k = linedata.nrad - 1; k != static_cast<Size>(-1); k--)
+                    if (inverted(k)) { set_LTE(temperature, p, k); modified_level[linedata.irad[k]] = true; modified_level[linedata.jrad[k]] = true; population_inversion_at_point = true; }
+                for (Size k = 0; k < linedata.nrad; k++)
+                    if (inverted(k)) { set_LTE(temperature, p, k); modified_level[linedata.irad[k]] = true; modified_level[linedata.jrad[k]] = true; population_inversion_at_point = true; }
+                if (population_inversion_at_point) set_LTE_specific_levels(temperature, p, modified_level);
+                next_n_modified_levels = std::accumulate(modified_level.begin(), modified_level.end(), static_cast<Size>(0));
+            } while (next_n_modified_levels != curr_n_modified_levels);
+        }
+    }
+};
+
+struct Image { // reference src/model/image/image.hpp (the fields the new imager fills)
+    Size nx = 0, ny = 0, nfreqs = 0;
+    double ray_direction[3] = {0, 0, 0};
+    std::vector<double> ImX, ImY, I, freqs; // I [nx*ny][nfreqs]
+};
+
+enum SpectralDiscretisation { SD_None, SD_Lines, SD_Image }; // model.hpp
+
+class Model {
+  public:
+    Parameters parameters;
+    // geometry (reference src/model/geometry): points, rays, boundary
+    Size npoints = 0, nrays = 0, nboundary = 0, nspecs = 0;
+    std::vector<double> position, velocity;      // [npoints][3]
+    std::vector<Size> n_neighbors, neighbors;
+    std::vector<double> direction, weight;       // [nrays][3], [nrays]
+    std::vector<Size> antipod, boundary2point, point2boundary;
+    std::vector<int32_t> boundary_condition;
+    std::vector<double> boundary_temperature;
+    // thermodynamics, chemistry
+    std::vector<Real> temperature_gas, vturb2, abundance; // abundance [npoints][nspecs]
+    // lines
+    std::vector<LineProducingSpecies> lineProducingSpecies;
+    std::vector<Size> nrad_cum;
+    std::vector<Real> line;                                  // [nlines] (Lines::line, lines.cpp:28-38)
+    std::vector<Real> emissivity, opacity, inverse_width;    // [npoints][nlines]
+    // radiation
+    Size nfreqs = 0;
+    std::vector<Real> nu, J;                                 // [npoints][nfreqs]
+    std::vector<Size> corresponding_line;
+    SpectralDiscretisation spectralDiscretisation = SD_None;
+    std::vector<Image> images;
+    std::vector<double> error_mean, error_max;
+    mgb_stats last_stats{};
+    double seconds_radiation_field = 0.0, seconds_statistical_equilibrium = 0.0; // Timer totals of model.cpp:706-724
+
+    Model() = default;
+    Model(const Model&) = delete;
+    Model& operator=(const Model&) = delete;
+    ~Model() { if (ctx) mgb_destroy(ctx); }
+
+    Size nlines() const { Size n = 0; for (auto& l : lineProducingSpecies) n += l.linedata.nrad; return n; }
+    Size nlspecs() const { return (Size)lineProducingSpecies.size(); }
+    Size nquads() const { return lineProducingSpecies.empty() ? 0 : (Size)lineProducingSpecies[0].quadrature_roots.size(); }
+    int device = 0;
+
+    // ---- set-up (what Model::read / the pybind setters establish in the reference) ----
+    void set_geometry(Size np, const double* pos, const double* vel, const Size* n_nbs, const Size* nbs, size_t n_nbs_tot, Size nr,
+                      const double* dir, const double* wgt, const Size* anti, Size nb, const Size* b2p, const int32_t* bcond,
+                      const double* btemp) {
+        npoints = np; nrays = nr; nboundary = nb;
+        position.assign(pos, pos + 3 * (size_t)np); velocity.assign(vel, vel + 3 * (size_t)np);
+        n_neighbors.assign(n_nbs, n_nbs + np); neighbors.assign(nbs, nbs + n_nbs_tot);
+        direction.assign(dir, dir + 3 * (size_t)nr); weight.assign(wgt, wgt + nr); antipod.assign(anti, anti + nr);
+        boundary2point.assign(b2p, b2p + nb);
+        point2boundary.assign(np, np); /* boundary.cpp:28-37: npoints marks an interior point */
+        for (Size b = 0; b < nb; b++) point2boundary[b2p[b]] = b;
+        boundary_condition.assign(bcond, bcond + nb); boundary_temperature.assign(btemp, btemp + nb);
+        dirty_geometry = true;
+    }
+    void set_thermodynamics(const double* T, const double* vt2) {
+        temperature_gas.assign(T, T + npoints); vturb2.assign(vt2, vt2 + npoints);
+        dirty_thermo = true;
+    }
+    void set_abundance(const double* ab, Size nsp) { nspecs = nsp; abundance.assign(ab, ab + (size_t)npoints * nsp); }
+    // Lines::read (lines.cpp:11-69): line list in species-major order
+    void add_species(LineProducingSpecies&& ls) {
+        lineProducingSpecies.push_back(std::move(ls));
+        finalize_lines();
+    }
+    void finalize_lines() {
+        nrad_cum.clear(); line.clear();
+        Size c = 0;
+        for (auto& l : lineProducingSpecies) {
+            l.parameters = &parameters; /* the vector may have moved */
+            nrad_cum.push_back(c); c += l.linedata.nrad;
+            for (Size k = 0; k < l.linedata.nrad; k++) line.push_back(l.linedata.frequency[k]);
+            if (l.npoints != npoints) l.resize(npoints);
+        }
+        emissivity.assign((size_t)npoints * c, 0); opacity = emissivity; inverse_width = emissivity;
+        dirty_lines = true;
+    }
+
+    Real profile_width(const Real inverse_mass, const Size p) const { // thermodynamics.tpp:32-35
+        return sqrt(TWO_KB_OVER_AMU_CC_SQUARED * inverse_mass * temperature_gas[p] + vturb2[p]);
+    }
+    // ---- Lines::set_inverse_width (lines.tpp:45-59) ----
+    int compute_inverse_line_widths() {
+        const Size L = nlines();
+        for (Size p = 0; p < npoints; p++)
+            for (Size l = 0; l < nlspecs(); l++)
+                for (Size k = 0; k < lineProducingSpecies[l].linedata.nrad; k++) {
+                    const Real invr_mass = lineProducingSpecies[l].linedata.inverse_mass;
+                    const Real frequency = lineProducingSpecies[l].linedata.frequency[k];
+                    inverse_width[(size_t)p * L + nrad_cum[l] + k] = (Real)1.0 / (frequency * profile_width(invr_mass, p));
+                }
+        return 0;
+    }
+    // ---- Lines::set_emissivity_and_opacity (lines.tpp:29-41) ----
+    void set_emissivity_and_opacity() {
+        const Size L = nlines();
+#pragma omp parallel for schedule(static)
+        for (Size p = 0; p < npoints; p++)
+            for (Size l = 0; l < nlspecs(); l++)
+                for (Size k = 0; k < lineProducingSpecies[l].linedata.nrad; k++) {
+                    emissivity[(size_t)p * L + nrad_cum[l] + k] = lineProducingSpecies[l].get_emissivity(p, k);
+                    opacity[(size_t)p * L + nrad_cum[l] + k]    = lineProducingSpecies[l].get_opacity(p, k);
+                }
+    }
+    // ---- Model::compute_spectral_discretisation() (model.cpp:70-161): f = lid*nquads + z ----
+    int compute_spectral_discretisation() {
+        const Size nq = nquads(), L = nlines();
+        nfreqs = L * nq;
+        nu.assign((size_t)npoints * nfreqs, 0); corresponding_line.assign(nfreqs, 0);
+        for (Size p = 0; p < npoints; p++) {
+            Size index0 = 0, index1 = 0;
+            for (Size l = 0; l < nlspecs(); l++) {
+                const Real inverse_mass = lineProducingSpecies[l].linedata.inverse_mass;
+                for (Size k = 0; k < lineProducingSpecies[l].linedata.nrad; k++) {
+                    const Real freqs_line = line[index0];
+                    const Real width      = freqs_line * profile_width(inverse_mass, p);
+                    for (Size z = 0; z < nq; z++) {
+                        const Real root = lineProducingSpecies[l].quadrature_roots[z];
+                        nu[(size_t)p * nfreqs + index1] = freqs_line + width * root;
+                        index1++;
+                    }
+                    index0++;
+                }
+            }
+        }
+        for (Size f = 0; f < nfreqs; f++) corresponding_line[f] = f / nq;
+        spectralDiscretisation = SD_Lines;
+        dirty_freqs = true;
+        return 0;
+    }
+    // ---- Model::compute_spectral_discretisation(nu_min, nu_max, n) (model.cpp:257-300): the same bins at every point ----
+    int compute_spectral_discretisation(const Real nu_min, const Real nu_max, const Size n_image_freqs) {
+        if (n_image_freqs < 1) throw std::runtime_error("At least a single frequency is needed to compute a spectral discretization.");
+        nfreqs = n_image_freqs;
+        image_nu.assign(nfreqs, 0);
+        if (n_image_freqs == 1) image_nu[0] = (Real)(nu_min + nu_max) / 2.0;
+        else {
+            const long double dnu = (nu_max - nu_min) / (n_image_freqs - 1);
+            for (Size f = 0; f < n_image_freqs; f++) image_nu[f] = (Real)(nu_min + f * dnu);
+        }
+        spectralDiscretisation = SD_Image;
+        return 0;
+    }
+    int compute_spectral_discretisation(const Real nu_min, const Real nu_max) { return compute_spectral_discretisation(nu_min, nu_max, nlines() * nquads()); }
+    std::vector<Real> image_nu;
+
+    // ---- Lines::iteration_using_LTE (lines.cpp:82-91) ----
+    int compute_LTE_level_populations() {
+        for (auto& lspec : lineProducingSpecies) lspec.update_using_LTE(abundance, nspecs, temperature_gas);
+        set_emissivity_and_opacity();
+        return 0;
+    }
+
+    int approx() const { // model.cpp:366-389
+        if (parameters.one_line_approximation) return MGB_APPROX_ONELINE;
+        if (parameters.sum_opacity_emissivity_over_all_lines) return MGB_APPROX_NONE;
+        return MGB_APPROX_CLOSELINES;
+    }
+    // ---- Model::compute_radiation_field_feautrier_order_2 (model.cpp:353-390) -> the C ABI ----
+    int compute_radiation_field_feautrier_order_2() {
+        sync_static(true);
+        const Size L = nlines();
+        J.resize((size_t)npoints * nfreqs);
+        std::vector<double> lam((size_t)npoints * L);
+        std::vector<uint32_t> cnt((size_t)npoints * L);
+        std::vector<double> ptot((size_t)nlspecs() * npoints);
+        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
+        check(mgb_solve_feautrier_order_2(ctx, approx(), emissivity.data(), opacity.data(), inverse_width.data(), ptot.data(), 0, npoints,
+                                          J.data(), lam.data(), cnt.data(), nullptr, &last_stats), "mgb_solve_feautrier_order_2");
+        for (Size l = 0; l < nlspecs(); l++) { /* Lambda lists per species: lambda.Ls[p][k], nr == p */
+            auto& ls = lineProducingSpecies[l];
+            const Size nrad = ls.linedata.nrad;
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    ls.lambda_Ls[(size_t)p * nrad + k]  = lam[(size_t)p * L + nrad_cum[l] + k];
+                    ls.lambda_cnt[(size_t)p * nrad + k] = cnt[(size_t)p * L + nrad_cum[l] + k];
+                }
+        }
+        return 0;
+    }
+    // ---- Model::compute_Jeff (model.cpp:514-545) ----
+    int compute_Jeff() {
+        const Size nq = nquads();
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& lspec = lineProducingSpecies[l];
+            const Size nrad = lspec.linedata.nrad;
+#pragma omp parallel for schedule(static)
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    Real jl = 0.0;
+                    for (Size z = 0; z < nq; z++) jl += lspec.quadrature_weights[z] * J[(size_t)p * nfreqs + (size_t)(nrad_cum[l] + k) * nq + z];
+                    double diff = 0.0;
+                    for (Size m = 0; m < lspec.lambda_cnt[(size_t)p * nrad + k]; m++) {
+                        const Size I = lspec.index(p, lspec.linedata.irad[k]);
+                        diff += lspec.lambda_Ls[(size_t)p * nrad + k] * lspec.population[I];
+                    }
+                    lspec.Jlin[(size_t)p * nrad + k] = jl;
+                    lspec.Jeff[(size_t)p * nrad + k] = jl - HH_OVER_FOUR_PI * diff;
+                    lspec.Jdif[(size_t)p * nrad + k] = HH_OVER_FOUR_PI * diff;
+                }
+        }
+        return 0;
+    }
+    // ---- Lines::iteration_using_statistical_equilibrium (lines.cpp:126-137) ----
+    int compute_level_populations_from_stateq() {
+        for (auto& lspec : lineProducingSpecies) {
+            lspec.update_using_statistical_equilibrium(abundance, nspecs, temperature_gas);
+            lspec.correct_negative_populations(temperature_gas);
+            lspec.check_for_convergence(parameters.pop_prec);
+        }
+        set_emissivity_and_opacity();
+        return 0;
+    }
+    void iteration_using_Ng_acceleration(const Size order) { // lines.cpp:106-117
+        for (auto& lspec : lineProducingSpecies) {
+            lspec.update_using_acceleration(order);
+            lspec.correct_negative_populations(temperature_gas);
+            lspec.check_for_convergence(parameters.pop_prec);
+        }
+        set_emissivity_and_opacity();
+    }
+    // model.cpp:580-653
+    std::tuple<bool, Size> ng_acceleration_criterion(const bool use_Ng_acceleration, const Size prior_normal_iterations) {
+        const Size skip_N_its = parameters.Ng_acceleration_remove_N_its;
+        if (!parameters.use_adaptive_Ng_acceleration) {
+            if (!use_Ng_acceleration) return std::make_tuple(false, 0u);
+            if (prior_normal_iterations == (parameters.Ng_acceleration_mem_limit + skip_N_its)) return std::make_tuple(true, parameters.Ng_acceleration_mem_limit);
+            return std::make_tuple(false, 0u);
+        }
+        if (!use_Ng_acceleration || prior_normal_iterations < parameters.adaptive_Ng_acceleration_min_order + skip_N_its) return std::make_tuple(false, 0u);
+        auto sum_fnc = [&]() {
+            double s = 0.0;
+            for (auto& l : lineProducingSpecies) s += parameters.adaptive_Ng_acceleration_use_max_criterion ? l.relative_change_max : l.relative_change_mean;
+            return s;
+        };
+        const double sum_fnc_curr = sum_fnc();
+        const Size nb_prev_iterations = prior_normal_iterations;
+        for (auto& lspec : lineProducingSpecies) { /* Lines::trial_iteration_using_adaptive_Ng_acceleration, lines.cpp:119-124 */
+            lspec.update_using_acceleration_trial(nb_prev_iterations - skip_N_its);
+            lspec.check_for_convergence_trial(parameters.pop_prec);
+        }
+        const double sum_fnc_ng = sum_fnc();
+        if ((sum_fnc_ng < sum_fnc_curr) || prior_normal_iterations == (parameters.Ng_acceleration_mem_limit + skip_N_its))
+            return std::make_tuple(true, nb_prev_iterations - skip_N_its);
+        return std::make_tuple(false, 0u);
+    }
+    // ---- Model::compute_level_populations (model.cpp:655-748) ----
+    int compute_level_populations(const bool use_Ng_acceleration, const long max_niterations) {
+        if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
+        int iteration = 0, iteration_normal = 0;
+        error_mean.clear(); error_max.clear();
+        bool some_not_converged = true;
+        while (some_not_converged && (iteration < max_niterations)) {
+            const auto decision = ng_acceleration_criterion(use_Ng_acceleration, (Size)iteration_normal);
+            if (std::get<0>(decision)) {
+                iteration_using_Ng_acceleration(std::get<1>(decision));
+                iteration_normal = 0;
+            } else {
+                iteration++;
+                some_not_converged = false;
+                const double t0 = now();
+                compute_radiation_field_feautrier_order_2();
+                compute_Jeff();
+                const double t1 = now();
+                compute_level_populations_from_stateq();
+                const double t2 = now();
+                seconds_radiation_field += t1 - t0; seconds_statistical_equilibrium += t2 - t1;
+                iteration_normal++;
+                for (auto& l : lineProducingSpecies) {
+                    error_mean.push_back(l.relative_change_mean);
+                    error_max.push_back(l.relative_change_max);
+                    if (l.fraction_not_converged > 1.0 - parameters.convergence_fraction) some_not_converged = true;
+                }
+            }
+        }
+        return iteration;
+    }
+    // ---- Model::compute_image_new(rx, ry, rz, Nxpix, Nypix) (model.cpp:999-1035) ----
+    int compute_image_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) {
+        if (rx * rx + ry * ry + rz * rz == 0.0)
+            throw std::runtime_error("The given ray direction vector does not point in a direction. Please use a non-zero (normed) direction vector to generate an image.");
+        if (parameters.one_line_approximation) throw std::runtime_error("One line approximation is not supported for imaging.");
+        sync_static(false);
+        Image im;
+        im.nx = Nxpix; im.ny = Nypix; im.nfreqs = nfreqs;
+        const double n = 1 / std::sqrt(rx * rx + ry * ry + rz * rz);
+        im.ray_direction[0] = rx * n; im.ray_direction[1] = ry * n; im.ray_direction[2] = rz * n;
+        const size_t npix = (size_t)Nxpix * Nypix;
+        im.ImX.resize(npix); im.ImY.resize(npix); im.I.resize(npix * nfreqs);
+        const double dir[3] = {rx, ry, rz};
+        const bool per_point = spectralDiscretisation == SD_Lines;
+        im.freqs = per_point ? std::vector<double>() : image_nu;
+        std::vector<double> ptot((size_t)nlspecs() * npoints);
+        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
+        check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+        check(mgb_image_feautrier_order_2(ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(),
+                                          per_point ? 1 : 0, 0, npix, im.ImX.data(), im.ImY.data(), im.I.data(), nullptr), "mgb_image_feautrier_order_2");
+        images.push_back(std::move(im));
+        return 0;
+    }
+
+  private:
+    mgb_ctx* ctx = nullptr;
+    bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true;
+    static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + 1e-9 * ts.tv_nsec; }
+    void check(int rc, const char* what) {
+        if (rc != MGB_OK) throw std::runtime_error(std::string(what) + " failed (" + std::to_string(rc) + "): " + mgb_last_error(ctx));
+    }
+    // Device context created lazily; static tables uploaded once and again only when the host arrays changed (SURVEY.md 8b "Ownership").
+    void sync_static(const bool need_line_freqs) {
+        if (!ctx) {
+            const int rc = mgb_create(device, &ctx);
+            if (rc != MGB_OK) { ctx = nullptr; throw std::runtime_error(std::string("mgb_create failed: ") + mgb_last_error(nullptr)); }
+        }
+        mgb_params prm;
+        mgb_params_default(&prm);
+        prm.min_opacity = parameters.min_opacity; prm.max_distance_opacity_contribution = parameters.max_distance_opacity_contribution;
+        prm.max_interpolation_diff = parameters.max_interpolation_diff; prm.max_width_fraction = parameters.max_width_fraction;
+        prm.n_off_diag = parameters.n_off_diag; prm.store_intensities = 0;
+        check(mgb_set_params(ctx, &prm), "mgb_set_params");
+        if (dirty_geometry) {
+            check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
+                                   direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
+                                   boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
+            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true;
+        }
+        if (dirty_thermo) { check(mgb_set_thermodynamics(ctx, temperature_gas.data(), vturb2.data()), "mgb_set_thermodynamics"); dirty_thermo = false; }
+        if (dirty_lines) {
+            std::vector<uint32_t> nrad; std::vector<double> im, A, qw;
+            for (auto& l : lineProducingSpecies) {
+                nrad.push_back(l.linedata.nrad); im.push_back(l.linedata.inverse_mass);
+                A.insert(A.end(), l.linedata.A.begin(), l.linedata.A.end());
+                qw.insert(qw.end(), l.quadrature_weights.begin(), l.quadrature_weights.end());
+            }
+            check(mgb_set_lines(ctx, nlspecs(), nrad.data(), im.data(), line.data(), A.data(), nquads(), qw.data()), "mgb_set_lines");
+            dirty_lines = false; dirty_freqs = true;
+        }
+        if (need_line_freqs) {
+            if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
+            if (dirty_freqs) { check(mgb_set_frequencies(ctx, nfreqs, nu.data(), corresponding_line.data()), "mgb_set_frequencies"); dirty_freqs = false; }
+        }
+    }
+};
+
+} // namespace mgbh

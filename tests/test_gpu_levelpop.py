@@ -1,0 +1,57 @@
+"""Model::compute_level_populations through the host layer (magritte_b200.core.Model -> C ABI -> CUDA) against the compiled
+reference (tests/golden/levelpop_*.pkl): K iterations without Ng acceleration at 1e-10, and the default adaptive-Ng run
+(same iteration count, populations at a looser bound because the Ng coefficients come from an ill-conditioned Gram matrix)."""
+import numpy as np
+import pytest
+
+import util
+from test_host_model import CASES, assert_populations_close, host_model
+
+pytestmark = pytest.mark.gpu
+
+
+def prepared(name):
+    m, flat, ref, lp = host_model(name)
+    m.compute_spectral_discretisation()
+    m.compute_inverse_line_widths()
+    m.compute_LTE_level_populations()
+    return m, flat, ref, lp
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_K_iterations_without_Ng(name):
+    m, flat, ref, lp = prepared(name)
+    m.mutable_parameters().use_adaptive_Ng_acceleration = False
+    it = m.compute_level_populations(False, lp["K"])
+    assert it == lp["K"]
+    for l, want in enumerate(lp["noNg_population"]):
+        assert_populations_close(m.get_population(l), want, m.get_population_tot(l), name)
+        assert util.relerr(m.get_Jeff(l), lp["noNg_Jeff"][l]) <= 1e-10
+    assert util.relerr(m.get_J()[::7], lp["noNg_J"]) <= 1e-10
+    assert np.allclose(m.error_max, lp["noNg_error_max"], rtol=1e-8, atol=1e-14)
+    assert m.seconds_radiation_field > 0
+
+
+@pytest.mark.parametrize("name", ["c1_all_constant", "c2_vanzadelhoff", "wind3d_small"])
+def test_default_adaptive_Ng_run(name):
+    m, flat, ref, lp = prepared(name)
+    it = m.compute_level_populations(True, 60)
+    assert it == lp["Ng_iterations"]
+    for l, want in enumerate(lp["Ng_population"]):
+        got = m.get_population(l)
+        want = want.reshape(got.shape)
+        tot = m.get_population_tot(l)[:, None]
+        assert np.all(np.abs(got - want) <= 1e-6 * np.abs(want) + 1e-12 * tot), name
+
+
+def test_image_through_host_model():
+    m, flat, ref, lp = prepared("wind3d_small")
+    fl, img = util.load_golden_image("wind3d_small")
+    nu = fl["nu_image"]
+    m.compute_spectral_discretisation(float(nu[0]), float(nu[-1]), len(nu))
+    d = img["directions"][1]
+    m.compute_image_new(float(d[0]), float(d[1]), float(d[2]), img["nx"], img["ny"])
+    X, Y, I = img["images"][1]
+    im = m.images[-1]
+    assert np.array_equal(im.ImX, X) and np.array_equal(im.ImY, Y)
+    assert util.relerr(im.I, I) <= 1e-10
