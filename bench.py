@@ -39,6 +39,10 @@ def parse():
     ap.add_argument("--nquads", type=int, default=11)
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-image", action="store_true", help="skip the imaging leg")
+    ap.add_argument("--image-pixels", type=int, default=512)
+    ap.add_argument("--image-freqs", type=int, default=100)
+    ap.add_argument("--no-levelpop", action="store_true", help="skip the level-population iteration leg (s_per_levelpop_iter)")
     ap.add_argument("--ref-pairs", type=int, default=1, help="ray pairs per step of the reference arm")
     return ap.parse_args()
 
@@ -197,6 +201,25 @@ def run_reference(args):
                                                       "sample": f"{R} ray pair(s) x {N} origins x {nfreqs} freqs per step; {how}"},
                       "e2e": {"value": val, "unit": "solves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                       "gpu_launches": 0}))
+
+
+def levelpop_iteration(args, flat, device):
+    """BASELINE.json's second metric: seconds per level-population iteration = radiation field + compute_Jeff + statistical
+    equilibrium (the reference's timer_1 + timer_2, model.cpp:706-724), through the host layer (magritte_b200.core.Model)."""
+    from magritte_b200 import model as hostmodel
+    spec = workload_spec(args)
+    m = hostmodel.from_spec(spec, flat, device, use_adaptive_Ng_acceleration=False)
+    m.compute_spectral_discretisation()
+    m.compute_inverse_line_widths()
+    m.compute_LTE_level_populations()
+    assert np.array_equal(m.get_emissivity(), flat["emissivity"]) and np.array_equal(m.get_nu(), flat["nu"])
+    t0 = time.perf_counter()
+    n = m.compute_level_populations(False, 2)
+    wall = time.perf_counter() - t0
+    return {"value": wall / n, "unit": "s/iteration", "iterations": n, "radiation_field_and_Jeff_s": m.seconds_radiation_field / n,
+            "statistical_equilibrium_s": m.seconds_statistical_equilibrium / n,
+            "note": "host-buffer path: H2D of the line state and D2H of J/Lambda every iteration; first iteration includes the ray trace; "
+                    "statistical equilibrium on the host cores (long double, OpenMP)"}
 
 
 def run_b200(args):
@@ -359,7 +382,33 @@ def run_b200(args):
             out["cpu_baseline"] = cpu_baseline_port(flat, args.cpu_seconds, approx)
         elif world == 1:
             out["cpu_baseline"] = None
+    # ---------------- imaging leg (BASELINE.json configs[4] shape on this model): pixels partitioned over the ranks ----------------
+    if not args.no_image:
+        nx = ny = args.image_pixels
+        nu0 = float(flat["line"][1])  # CO J=2-1
+        dv = 20.0e3 / 2.99792458e8
+        nu_img = np.linspace(nu0 * (1 - dv), nu0 * (1 + dv), args.image_freqs)
+        npix = nx * ny
+        p0, p1 = npix * rank // world, npix * (rank + 1) // world
+        ctx.image(2, 3, (0.3, 0.5, 0.81), nx, ny, nu_img, pix_range=(p0, p1))  # warm-up
+        sync()
+        if dist is not None:
+            dist.barrier()
+        ctx.timer_start()
+        t0 = time.perf_counter()
+        for d in [(1.0, 0.0, 0.0), (0.3, 0.5, 0.81)]:
+            _, _, I_img, ist = ctx.image(2, 3, d, nx, ny, nu_img, pix_range=(p0, p1))
+        ms_img = max(ctx.timer_stop(), (time.perf_counter() - t0) * 1e3)
+        ms_img = max_over_ranks(ms_img) / 2
+        if out is not None:
+            out["image"] = {"metric": "pixel*freq image solves/s (Solver::image_feautrier_order_2_new_imager)", "value": npix * args.image_freqs / (ms_img * 1e-3),
+                            "unit": "solves/s", "ms_per_image": ms_img, "pixels": [nx, ny], "nfreqs": args.image_freqs,
+                            "kernel_ms": {"trace": ist.ms_trace, "solve": ist.ms_solve}, "entries_per_pixel": ist.n_entries / max(1, ist.n_pixels),
+                            "note": "end to end through mgb_image_feautrier_order_2 with host buffers (D2H of the image inside the timed region); "
+                                    f"{flat['npoints']}-point model of this bench (the 10M-point cloud of configs[4] is not generated here); pixels/{world} per rank"}
     ctx.close()
+    if out is not None and world == 1 and not args.no_levelpop:
+        out["s_per_levelpop_iter"] = levelpop_iteration(args, flat, local)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

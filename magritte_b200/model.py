@@ -73,3 +73,32 @@ def from_reference(model, device=0):
     flat = flatten.flatten_model(model, with_state=False)
     ab = np.array(model.chemistry.species.abundance, dtype=np.float64)
     return build(flat, linedata_of(model), ab, parameters_of(model), device)
+
+
+def species_from_spec(spec):
+    """The `species` list of build() from a modelbuild spec (parsed LAMDA dicts; same mapping as modelbuild.set_linedata)."""
+    from .modelbuild import gauss_hermite
+    roots, weights = gauss_hermite(int(spec["nquads"]))
+    symbols = list(spec["symbols"])
+    out = []
+    for ld in spec["linedata"]:
+        d = dict(num=symbols.index(ld["sym"]), nlev=int(ld["nlev"]), nrad=int(ld["nrad"]), inverse_mass=float(ld["inverse_mass"]),
+                 irad=np.asarray(ld["irad"], dtype=np.uint32), jrad=np.asarray(ld["jrad"], dtype=np.uint32),
+                 energy=np.asarray(ld["energy"], dtype=np.float64), weight=np.asarray(ld["weight"], dtype=np.float64),
+                 frequency=np.asarray(ld["frequency"], dtype=np.float64), A=np.asarray(ld["A"], dtype=np.float64),
+                 Ba=np.asarray(ld["Ba"], dtype=np.float64), Bs=np.asarray(ld["Bs"], dtype=np.float64),
+                 quadrature_roots=np.asarray(roots, dtype=np.float64), quadrature_weights=np.asarray(weights, dtype=np.float64), colpar=[])
+        for cp in ld["colpar"]:
+            d["colpar"].append(dict(num_col_partner=symbols.index(cp["name"]) if cp["name"] in symbols else 0,
+                                    orth_or_para_H2=str(cp["orth_or_para_H2"]), icol=np.asarray(cp["icol"], dtype=np.uint32),
+                                    jcol=np.asarray(cp["jcol"], dtype=np.uint32), tmp=np.asarray(cp["tmp"], dtype=np.float64),
+                                    Ce=np.asarray(cp["Ce"], dtype=np.float64), Cd=np.asarray(cp["Cd"], dtype=np.float64)))
+        out.append(d)
+    return out
+
+
+def from_spec(spec, flat, device=0, **parameters):
+    """Host Model of a synthetic modelbuild spec (bench.py's level-population leg); flat = synth.flat_from_spec(spec)."""
+    prm = dict(spherical_symmetry=bool(spec["spherical"]), dimension=int(spec.get("dimension", 1 if spec["spherical"] else 3)))
+    prm.update(parameters)
+    return build(flat, species_from_spec(spec), np.asarray(spec["abundance"], dtype=np.float64), prm, device)
