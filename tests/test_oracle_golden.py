@@ -45,3 +45,14 @@ def test_oracle_image_bit_exact(name):
         r = o.image(d, img["nx"], img["ny"], img["dimension"])
         assert np.array_equal(r["ImX"], X) and np.array_equal(r["ImY"], Y)
         assert np.array_equal(r["I"], I), f"{name} {d}: max rel err {util.relerr(r['I'], I)}"
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_oracle_banded_lambda_bit_exact(name):
+    """n_off_diag > 0: the oracle's Lambda lists equal the compiled reference's, element for element in insertion order."""
+    flat, ref = util.load_golden_offdiag(name)
+    o = orc.Oracle(flat, store_u=False)
+    J = o.solve()
+    assert np.array_equal(J, ref["J"])
+    cap = ref["lambda_nr"].shape[2]
+    util.lambda_lists_close(o.L_val[:, :, :cap], o.L_nr[:, :, :cap], o.L_cnt, ref, 0)

@@ -117,3 +117,32 @@ def load_golden_image(name):
     img = dict(dimension=int(z["dimension"]), nx=int(z["nx"]), ny=int(z["ny"]), directions=dirs,
                images=[(z[f"ImX_{i}"], z[f"ImY_{i}"], z[f"I_{i}"]) for i in range(len(dirs))])
     return flat, img
+
+
+def load_golden_offdiag(name):
+    """-> (flat inputs with params.n_off_diag = K, dict(J, lambda_val/nr/cnt [N][L][cap] in the reference's insertion order))."""
+    flat, _ = load_golden(name)
+    z = np.load(os.path.join(GOLDEN, f"offdiag_{name}.npz"))
+    flat["params"] = dict(flat["params"], n_off_diag=int(z["n_off_diag"]))
+    return flat, {k: z[k] for k in ("J", "lambda_val", "lambda_nr", "lambda_cnt")}
+
+
+def lambda_lists_close(val, nr, cnt, ref, tol):
+    """Compare (p, line) lists after sorting by nr (SURVEY.md 8c protocol); tol = 0 demands identical bits in insertion order."""
+    assert np.array_equal(cnt, ref["lambda_cnt"]), "list lengths differ"
+    N, L = cnt.shape
+    cap = ref["lambda_nr"].shape[2]
+    worst = 0.0
+    for p in range(N):
+        for l in range(L):
+            c = int(cnt[p, l])
+            a_nr, a_v = nr[p, l, :c], val[p, l, :c]
+            b_nr, b_v = ref["lambda_nr"][p, l, :c], ref["lambda_val"][p, l, :c]
+            if tol == 0:
+                assert np.array_equal(a_nr, b_nr) and np.array_equal(a_v, b_v), (p, l)
+                continue
+            ia, ib = np.argsort(a_nr, kind="stable"), np.argsort(b_nr, kind="stable")
+            assert np.array_equal(a_nr[ia], b_nr[ib]), (p, l)
+            worst = max(worst, relerr(a_v[ia], b_v[ib]))
+    assert worst <= tol, worst
+    return worst
