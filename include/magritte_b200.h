@@ -44,7 +44,7 @@ typedef struct mgb_params {
     double max_distance_opacity_contribution; /* = 10 (CloseLines window, solver.tpp:1219) */
     double max_interpolation_diff;            /* = 1.4 (sub-step criterion, solver_interp_helper.tpp:68) */
     double max_width_fraction;                /* = 0.35 (Model::set_dshift_max, model.cpp:1158-1178) */
-    uint32_t n_off_diag;                      /* = 0; >0 not yet supported (MGB_EUNSUPPORTED) */
+    uint32_t n_off_diag;                      /* = 0; banded Lambda operator up to 4 off-diagonals (results: mgb_get_lambda_lists) */
     uint32_t store_intensities;               /* keep u(rr,o,f) (Radiation::u, solver.tpp:461-465,503) */
     /* implementation knobs (no reference counterpart) */
     uint64_t path_cache_bytes;                /* HBM budget for cached ray paths; 0 = library default */
@@ -123,6 +123,12 @@ int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32
 int mgb_get_J(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J);
 int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* lambda_val, uint32_t* lambda_cnt);
 int mgb_get_u(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* u);
+/* n_off_diag = K > 0 (banded approximate Lambda operator, Solver::update_Lambda solver.tpp:1806-1850 with L_lower/L_upper of
+ * :2320-2355): the (p, line) lists of Lambda::add_element (lambda.tpp:79-89) in the reference's insertion order.
+ * capacity = 1 + 2*K*hnrays entries per list; list_val / list_nr [(o_end-o_begin)][nlines][capacity] (unused tail: 0 / 0xffffffff),
+ * list_cnt [(o_end-o_begin)][nlines]. With K > 0 mgb_get_lambda returns the diagonal element and the list length. */
+int mgb_lambda_capacity(mgb_ctx* ctx, uint32_t* capacity);
+int mgb_get_lambda_lists(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* list_val, uint32_t* list_nr, uint32_t* list_cnt);
 /* One call, host buffers in and out (what Model::compute_radiation_field_feautrier_order_2 binds):
  * mgb_set_line_state + mgb_run + mgb_get_J + mgb_get_lambda (+ mgb_get_u if u != NULL). */
 int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const double* emissivity, const double* opacity,

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("MGB_LIB") or os.path.join(_HERE, "lib", "libmagritte_
 EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
-    "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_solve_feautrier_order_2",
+    "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
     "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv",
 ]
@@ -193,6 +193,18 @@ class Context:
                                                        C.byref(st)), "mgb_run_feautrier_order_2")
         self.last_range = (o0, o1)
         return st
+
+    def get_lambda_lists(self, o_range=None):
+        """n_off_diag > 0: (val [rows][nlines][cap], nr, cnt) -- the reference's (p, line) lists in insertion order."""
+        o0, o1 = o_range or self.last_range
+        cap = C.c_uint32()
+        self._check(self.lib.mgb_lambda_capacity(self._ctx, C.byref(cap)), "mgb_lambda_capacity")
+        val = np.empty((o1 - o0, self.nlines, cap.value))
+        nr = np.empty((o1 - o0, self.nlines, cap.value), dtype=np.uint32)
+        cnt = np.empty((o1 - o0, self.nlines), dtype=np.uint32)
+        self._check(self.lib.mgb_get_lambda_lists(self._ctx, C.c_uint32(o0), C.c_uint32(o1), val.ctypes.data_as(C.c_void_p),
+                                                  nr.ctypes.data_as(C.c_void_p), cnt.ctypes.data_as(C.c_void_p)), "mgb_get_lambda_lists")
+        return val, nr, cnt
 
     def get_J(self, o_range=None):
         o0, o1 = o_range or self.last_range

@@ -83,7 +83,7 @@ extern "C" const char* mgb_last_error(const mgb_ctx* ctx) { return ctx ? ctx->er
 
 extern "C" int mgb_set_params(mgb_ctx* ctx, const mgb_params* p) {
     if (!ctx || !p) return MGB_EINVAL;
-    if (p->n_off_diag != 0) return ctx->fail(MGB_EUNSUPPORTED, "n_off_diag > 0 (banded Lambda operator) is not implemented");
+    if (p->n_off_diag > (uint32_t)kMaxOffDiag) return ctx->fail(MGB_EUNSUPPORTED, "n_off_diag = %u: at most %d off-diagonals are supported", p->n_off_diag, kMaxOffDiag);
     if (p->max_width_fraction != ctx->params.max_width_fraction) ctx->points_dirty = true;
     ctx->params = *p;
     if (ctx->params.path_cache_bytes == 0) ctx->params.path_cache_bytes = 48ull << 30;
@@ -395,16 +395,20 @@ int fill_chunk(mgb_ctx* ctx, PathChunk& ch, mgb_stats* st, uint32_t& launches) {
     return MGB_OK;
 }
 
-template <int APPROX>
-cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
+template <int APPROX, bool OFFD>
+cudaError_t launch_solve2(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
     const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
     const size_t blocks = (nitems * 32 + 127) / 128;
     const size_t smem   = 4 * solve_smem_per_warp(ctx->lines_per_warp);
-    cudaError_t e = cudaFuncSetAttribute(k_solve<APPROX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t e = cudaFuncSetAttribute(k_solve<APPROX, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    k_solve<APPROX><<<(unsigned)blocks, 128, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
-                                                                  ctx->lines_per_warp);
+    k_solve<APPROX, OFFD><<<(unsigned)blocks, 128, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
+                                                                        ctx->lines_per_warp);
     return cudaGetLastError();
+}
+template <int APPROX>
+cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
+    return sc.K ? launch_solve2<APPROX, true>(ctx, pv, sc, nchunks_f) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
 }
 
 } // namespace
@@ -472,7 +476,6 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     if (approx < 0 || approx > 2) return ctx->fail(MGB_EINVAL, "approx must be 0 (None), 1 (OneLine) or 2 (CloseLines)");
     DevModel& m = ctx->m;
     if (o_begin >= o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "origin range [%u,%u) invalid for npoints = %u", o_begin, o_end, m.npoints);
-    if (ctx->params.n_off_diag) return ctx->fail(MGB_EUNSUPPORTED, "n_off_diag > 0 is not implemented");
     cudaSetDevice(ctx->device);
     mgb_stats st;
     memset(&st, 0, sizeof st);
@@ -484,7 +487,8 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
 
     const uint32_t nchunks_f = ctx->n_freq_chunks;
     // ---- plan origin chunks: bounded scratch (16 B per solve) and bounded path bytes (20 B per step) ----
-    const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * 16;
+    const uint32_t K = ctx->params.n_off_diag;
+    const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * (16 + 24 * (size_t)K);
     const uint32_t max_o_scratch    = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / per_origin_scratch);
     unsigned long long range_steps  = 0;
     for (uint32_t o = o_begin; o < o_end; o++) range_steps += ctx->origin_steps[o - ctx->lens_o0];
@@ -524,6 +528,13 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     MGB_CUDA(ctx, ctx->scratch_L.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
     MGB_CUDA(ctx, ctx->counters.ensure(64));
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+    if (K) { /* banded operator: at most 1 + 2K distinct points per ray pair (lambda.tpp:79-89 lists) */
+        ctx->lam_cap = 1 + 2 * K * m.hnrays;
+        MGB_CUDA(ctx, ctx->lam_list_val.ensure(8 * prow * m.nlines * ctx->lam_cap));
+        MGB_CUDA(ctx, ctx->lam_list_nr.ensure(4 * prow * m.nlines * ctx->lam_cap));
+        MGB_CUDA(ctx, ctx->scratch_offV.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs * 2 * K));
+        MGB_CUDA(ctx, ctx->scratch_offN.ensure(4 * (size_t)m.hnrays * max_no * m.nfreqs * 2 * K));
+    } else ctx->lam_cap = 1;
 
     bool all_cached = true;
     for (auto* cp : ctx->chunks) {
@@ -537,7 +548,8 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         PathView pv{};
         pv.o0 = ch->o0; pv.no = no; pv.len = ctx->lens.as<uint32_t>(); pv.poff = ch->poff.as<unsigned long long>();
         pv.nr = ch->nr.as<uint32_t>(); pv.dZ = ch->dZ.as<double>(); pv.shift = ch->shift.as<double>(); pv.shift0 = ch->shift0.as<double>();
-        ScratchView sc{ctx->scratch_u.as<double>(), ctx->scratch_L.as<double>(), ctx->counters.as<unsigned long long>()};
+        ScratchView sc{ctx->scratch_u.as<double>(), ctx->scratch_L.as<double>(), ctx->counters.as<unsigned long long>(),
+                       ctx->scratch_offV.as<double>(), ctx->scratch_offN.as<uint32_t>(), K};
         EventTimer ts(ctx->stream);
         ts.start();
         if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f));
@@ -550,17 +562,23 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         tr.start();
         const size_t nj = (size_t)no * m.nfreqs, nl = (size_t)no * m.nlines;
         k_reduce_J<<<(unsigned)((nj + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J.as<double>(), u_full, ctx->u_o0, ctx->u_no);
-        k_reduce_lambda<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.L,
-                                                                               ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
+        if (K)
+            k_reduce_lambda_banded<<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(
+                m, ch->o0, no, K, ctx->lam_cap, ctx->lens.as<uint32_t>(), sc.L, sc.offV, sc.offN, ctx->lam_list_val.as<double>(),
+                ctx->lam_list_nr.as<uint32_t>(), ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>(), ctx->counters.as<unsigned long long>() + 4);
+        else
+            k_reduce_lambda<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.L,
+                                                                                   ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
         MGB_CUDA(ctx, cudaGetLastError());
         st.ms_reduce += tr.stop();
         launches += 2;
     }
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     st.ms_total = total.stop();
-    unsigned long long c[2];
-    MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 16, cudaMemcpyDeviceToHost));
+    unsigned long long c[5];
+    MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 40, cudaMemcpyDeviceToHost));
     st.n_entries = c[0]; st.n_large_shift = c[1];
+    if (K && c[4]) return ctx->fail(MGB_ENOMEM, "banded Lambda operator: %llu list insertions exceeded the capacity %u", c[4], ctx->lam_cap);
     st.n_steps = range_steps;
     st.n_nbs_scanned = ctx->tot_scanned; /* of the counted range */
     st.n_solves = (uint64_t)(o_end - o_begin) * m.hnrays * m.nfreqs;
@@ -597,6 +615,24 @@ extern "C" int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, do
     const size_t L = ctx->m.nlines, n = (size_t)(o_end - o_begin) * L;
     MGB_CUDA(ctx, cudaMemcpy(lambda_val, ctx->lam_val.as<double>() + (size_t)o_begin * L, 8 * n, cudaMemcpyDeviceToHost));
     MGB_CUDA(ctx, cudaMemcpy(lambda_cnt, ctx->lam_cnt.as<uint32_t>() + (size_t)o_begin * L, 4 * n, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_lambda_capacity(mgb_ctx* ctx, uint32_t* cap) {
+    if (!ctx || !cap) return MGB_EINVAL;
+    *cap = ctx->params.n_off_diag ? 1 + 2 * ctx->params.n_off_diag * ctx->m.hnrays : 1;
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_lambda_lists(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* list_val, uint32_t* list_nr, uint32_t* list_cnt) {
+    if (!ctx || !list_val || !list_nr || !list_cnt) return MGB_EINVAL;
+    MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_lambda_lists"));
+    if (!ctx->params.n_off_diag || !ctx->lam_list_val.p) return ctx->fail(MGB_ESTATE, "mgb_get_lambda_lists: the last run had n_off_diag = 0 (use mgb_get_lambda)");
+    cudaSetDevice(ctx->device);
+    const size_t L = ctx->m.nlines, n = (size_t)(o_end - o_begin) * L, cap = ctx->lam_cap;
+    MGB_CUDA(ctx, cudaMemcpy(list_val, ctx->lam_list_val.as<double>() + (size_t)o_begin * L * cap, 8 * n * cap, cudaMemcpyDeviceToHost));
+    MGB_CUDA(ctx, cudaMemcpy(list_nr, ctx->lam_list_nr.as<uint32_t>() + (size_t)o_begin * L * cap, 4 * n * cap, cudaMemcpyDeviceToHost));
+    MGB_CUDA(ctx, cudaMemcpy(list_cnt, ctx->lam_cnt.as<uint32_t>() + (size_t)o_begin * L, 4 * n, cudaMemcpyDeviceToHost));
     return MGB_OK;
 }
 

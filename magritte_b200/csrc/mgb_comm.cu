@@ -87,6 +87,7 @@ extern "C" int mgb_partition(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_beg
 }
 
 extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
+    if (ctx && ctx->params.n_off_diag) return ctx->fail(MGB_EUNSUPPORTED, "mgb_allgather_results: the banded Lambda lists (n_off_diag > 0) are gathered by the host (mgb_get_lambda_lists per rank)");
     if (!ctx) return MGB_EINVAL;
     if (ctx->nranks == 1) return MGB_OK;
     if (!ctx->comm) return ctx->fail(MGB_ESTATE, "mgb_allgather_results: mgb_comm_init was not called");

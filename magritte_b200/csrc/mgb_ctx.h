@@ -67,6 +67,8 @@ struct mgb_ctx {
     mgb::DevBuf stage_a, stage_b, stage_c, stage_d; // H2D staging of the per-iteration line state
     // results
     mgb::DevBuf J, lam_val, lam_cnt, u_full;
+    mgb::DevBuf lam_list_val, lam_list_nr, scratch_offV, scratch_offN; // banded Lambda operator (n_off_diag > 0)
+    uint32_t lam_cap = 1;
     uint32_t u_o0 = 0, u_no = 0;
     uint32_t res_o0 = 0, res_o1 = 0; // origin range of the last run
     // tracing state

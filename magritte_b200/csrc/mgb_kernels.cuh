@@ -25,7 +25,13 @@ struct ScratchView {
     double* u;     // [hnrays][no][nfreqs]   Su[centre] (or the boundary intensity for an isolated origin)
     double* L;     // [hnrays][no][nfreqs]   the Lambda increment of (rr, o, f)
     unsigned long long* counters; // [0] entries (Sigma N), [1] large-shift segment evaluations
+    // banded Lambda operator (n_off_diag = K > 0): per (rr, o, f) the 2K off-diagonal increments in the order update_Lambda adds
+    // them (m = 0..K-1: lower, upper), and the point each belongs to (0xffffffff: no such element)
+    double* offV;   // [hnrays][no][nfreqs][2K]
+    uint32_t* offN; // [hnrays][no][nfreqs][2K]
+    uint32_t K;
 };
+constexpr int kMaxOffDiag = 4; // largest supported n_off_diag
 
 // ---------------------------------------------------------------------------------------------------
 __global__ void k_prepare_rows(uint32_t npoints, uint32_t nlines, const double* __restrict__ emis, const double* __restrict__ opac,

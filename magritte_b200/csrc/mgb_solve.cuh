@@ -515,8 +515,23 @@ __device__ __forceinline__ void produce_centre(const DevModel& m, const WarpSmem
 }
 
 // ---------------------------------------------------------------------------------------------------
-template <int APPROX>
-__global__ void __launch_bounds__(128, 4) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
+// History of the rows eliminated last on one side (nearest the origin first when read back): what the banded Lambda operator
+// needs of the entries within n_off_diag of the origin. Ring buffers in local memory; only the OFFD instantiation has them.
+struct SideHistory {
+    static constexpr int R = kMaxOffDiag + 2;
+    double F[R], FI[R], D[R], sh[R]; // FF/FI (side 0) or GG/GI (side 1) of the row, dtau of its segment towards the origin, shift
+    uint32_t nr[R];
+    unsigned cnt;
+    __device__ __forceinline__ void push(double f, double fi, double d, uint32_t p, double s) {
+        const unsigned i = cnt % R;
+        F[i] = f; FI[i] = fi; D[i] = d; nr[i] = p; sh[i] = s;
+        cnt++;
+    }
+    __device__ __forceinline__ unsigned slot(unsigned j) const { return (cnt - 1u - j) % R; } // j-th nearest to the origin
+};
+
+template <int APPROX, bool OFFD>
+__global__ void __launch_bounds__(128, OFFD ? 2 : 4) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
                                                   const FreqChunk* __restrict__ chunks, uint32_t nchunks_f, uint32_t lpw) {
     const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -570,6 +585,8 @@ __global__ void __launch_bounds__(128, 4) k_solve(const __grid_constant__ DevMod
     const double* rb   = ws.rec(ks) + 1; /* entry e of this lane's line */
     const uint32_t* eo = ws.eoff(ks);
 
+    SideHistory hist[OFFD ? 2 : 1];
+    if (OFFD) { hist[0].cnt = 0; hist[1].cnt = 0; }
     for (int side = 0; side < 2; side++) {
         const uint32_t r   = side ? ar : rr;
         const uint32_t len = side ? len_f : len_b;
@@ -598,8 +615,13 @@ __global__ void __launch_bounds__(128, 4) k_solve(const __grid_constant__ DevMod
                 for (uint32_t it = 0; it < nmax; it++) {
                     const bool part = it < ns;
                     const double* q = rb + e0 + (part ? it : 0u);
+                    const bool hadX = st.haveX;
                     if (!sweep_step_common<APPROX>(m, L, st, side, q, freq, part)) {
                         if (part) st = sweep_step_general<APPROX>(m, L, st, side, q, ll, freq);
+                    }
+                    if (OFFD && part && hadX) { /* the row of X = q[-1] has just been eliminated */
+                        const uint2 pX = *reinterpret_cast<const uint2*>(&MGB_REC(q - 1, R_PTS));
+                        hist[OFFD ? side : 0].push(st.F, st.FI, st.dtau_far, pX.x, MGB_REC(q - 1, R_SHIFT));
                     }
                 }
             }
@@ -665,6 +687,97 @@ __global__ void __launch_bounds__(128, 4) k_solve(const __grid_constant__ DevMod
 
     if (active) { sc.u[out] = u; sc.L[out] = Lam; }
 
+    if (OFFD) {
+        // ---- off-diagonal elements of the banded Lambda operator (solver.tpp:2320-2355 and update_Lambda :1806-1850) ----
+        // Index i counts entries from the origin: i < 0 towards `first`, i > 0 towards `last`; n0 / n1 entries on the two sides.
+        // FF, FI of i < 0 and GG, GI of i > 0 are the rows the two sweeps eliminated last (hist); the forward recursion is continued
+        // across the origin to i = K and the backward one to i = -K+1 with the reference's formulas, then
+        //   L_lower(m, -m-1) = L_diag[-m-1] * GI[-m] * ... * GI[0],   L_upper(m, m+1) = L_diag[m+1] * FI[m] * ... * FI[0].
+        constexpr int KM = kMaxOffDiag;
+        const int K  = (int)sc.K;
+        const int n0 = (int)hist[0].cnt, n1 = (int)hist[OFFD ? 1 : 0].cnt;
+        const SideHistory& H0 = hist[0];
+        const SideHistory& H1 = hist[OFFD ? 1 : 0];
+        auto seg = [&](int i) -> double { return i < 0 ? H0.D[H0.slot((unsigned)(-i - 1))] : H1.D[H1.slot((unsigned)i)]; }; /* dtau(i, i+1) */
+        double FFw[2 * KM + 3], FIw[2 * KM + 3], GGw[2 * KM + 3], GIw[2 * KM + 3]; /* index i + KM + 1 */
+        for (int i = -1; i >= -K - 1 && i >= -n0; i--) { FFw[i + KM + 1] = H0.F[H0.slot((unsigned)(-i - 1))]; FIw[i + KM + 1] = H0.FI[H0.slot((unsigned)(-i - 1))]; }
+        for (int i = 1; i <= K + 1 && i <= n1; i++) { GGw[i + KM + 1] = H1.F[H1.slot((unsigned)(i - 1))]; GIw[i + KM + 1] = H1.FI[H1.slot((unsigned)(i - 1))]; }
+        for (int i = 0; i <= K && i < n1; i++) { /* FF exists for first <= n < last */
+            double FFi;
+            if (i == -n0) { /* the origin is `first` */
+                const double dt = seg(0), inv = 1.0 / dt;
+                const double Bm = 1.0 + 2.0 * inv;
+                FFi = 0.5 * Bm * dt * dt;
+            } else {
+                const double avg = 0.5 * (seg(i - 1) + seg(i));
+                const double invA = avg * seg(i - 1), invC = avg * seg(i);
+                const double A = 1.0 / invA;
+                FFi = (A * FFw[i - 1 + KM + 1] * FIw[i - 1 + KM + 1] + 1.0) * invC;
+            }
+            FFw[i + KM + 1] = FFi; FIw[i + KM + 1] = 1.0 / (1.0 + FFi);
+        }
+        for (int i = 0; i >= -K + 1 && i > -n0; i--) { /* GG exists for first < n <= last */
+            double GGi;
+            if (i == n1) { /* the origin is `last` */
+                const double dt = seg(-1), inv = 1.0 / dt;
+                const double Bm = 1.0 + 2.0 * inv;
+                GGi = 0.5 * Bm * dt * dt;
+            } else {
+                const double avg = 0.5 * (seg(i - 1) + seg(i));
+                const double invA = avg * seg(i - 1), invC = avg * seg(i);
+                const double C = 1.0 / invC;
+                GGi = (C * (GGw[i + 1 + KM + 1] * GIw[i + 1 + KM + 1]) + 1.0) * invA;
+            }
+            GGw[i + KM + 1] = GGi; GIw[i + KM + 1] = 1.0 / (1.0 + GGi);
+        }
+        auto Ldiag_at = [&](int n) -> double {
+            if (n == -n0) { /* first (solver.tpp:2335) */
+                const double inv = 1.0 / seg(n);
+                const double Cf = 2.0 * inv * inv, Bm = 1.0 + 2.0 * inv, Bf = Bm + Cf;
+                return (1.0 + GGw[n + 1 + KM + 1]) / (Bm + Bf * GGw[n + 1 + KM + 1]);
+            }
+            if (n == n1) { /* last (solver.tpp:2324) */
+                const double inv = 1.0 / seg(n - 1);
+                const double Al = 2.0 * inv * inv, Bm = 1.0 + 2.0 * inv, Bl = Bm + Al;
+                return (1.0 + FFw[n - 1 + KM + 1]) / (Bm + Bl * FFw[n - 1 + KM + 1]);
+            }
+            const double avg = 0.5 * (seg(n - 1) + seg(n));
+            const double invC = avg * seg(n);
+            return invC / (FFw[n + KM + 1] + GGw[n + 1 + KM + 1] * GIw[n + 1 + KM + 1]);
+        };
+        auto element = [&](uint32_t p, double shift_n, double Lband) -> double { /* update_Lambda :1816-1826 / :1838-1845 */
+            double eta_n, chi_n;
+            eta_chi_generic<APPROX>(m, p, p, 0.0, __ldg(&m.line_k[l]), freq_line, eta_n, chi_n);
+            const double ichi = 1.0 / chi_n;
+            const double fq   = __ldg(&m.nu[(size_t)p * m.nfreqs + f]) * shift_n;
+            const double ph   = thermo_profile(m, __ldg(&m.line_invmass[l]), p, freq_line, fq);
+            return constante * fq * ph * Lband * ichi;
+        };
+        double lowprod = 1.0, upprod = 1.0;
+        for (int mm = 0; mm < K; mm++) {
+            double vl = 0.0, vu = 0.0;
+            uint32_t pl = 0xffffffffu, pu = 0xffffffffu;
+            if (n0 >= mm + 1) {
+                const int n = -mm - 1;
+                lowprod *= GIw[n + 1 + KM + 1]; /* GI[-m] joins the product */
+                const unsigned sl = H0.slot((unsigned)mm);
+                pl = H0.nr[sl];
+                vl = element(pl, H0.sh[sl], Ldiag_at(n) * lowprod);
+            }
+            if (n1 >= mm + 1) {
+                const int n = mm + 1;
+                upprod *= FIw[n - 1 + KM + 1]; /* FI[m] joins the product */
+                const unsigned su = H1.slot((unsigned)mm);
+                pu = H1.nr[su];
+                vu = element(pu, H1.sh[su], Ldiag_at(n) * upprod);
+            }
+            if (active) {
+                sc.offV[(out * K + mm) * 2] = vl; sc.offN[(out * K + mm) * 2] = pl;
+                sc.offV[(out * K + mm) * 2 + 1] = vu; sc.offN[(out * K + mm) * 2 + 1] = pu;
+            }
+        }
+    }
+
     // work counters: Sigma N counts one ray per (o, rr, line); large-shift evaluations per lane
     unsigned e = (active && z == 0) ? nentries : 0u;
     unsigned g = active ? nlarge : 0u;
@@ -713,6 +826,43 @@ __global__ void k_reduce_lambda(DevModel m, uint32_t o0, uint32_t no, const uint
         }
     }
     lam_val[(size_t)o * m.nlines + l] = acc;
+    lam_cnt[(size_t)o * m.nlines + l] = cnt;
+}
+
+// Banded operator: the (p = o, line) list of (nr, Ls) built exactly as Lambda::add_element does (lambda.tpp:79-89) while
+// update_Lambda runs over rr > z > (diagonal, then m = 0..K-1: lower, upper) (solver.tpp:476-508, 1806-1850).
+__global__ void k_reduce_lambda_banded(DevModel m, uint32_t o0, uint32_t no, uint32_t K, uint32_t cap, const uint32_t* __restrict__ lens,
+                                       const double* __restrict__ L, const double* __restrict__ offV, const uint32_t* __restrict__ offN,
+                                       double* __restrict__ list_val, uint32_t* __restrict__ list_nr, double* __restrict__ lam_val,
+                                       uint32_t* __restrict__ lam_cnt, unsigned long long* __restrict__ overflow) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)no * m.nlines) return;
+    const uint32_t ol = (uint32_t)(i / m.nlines), l = (uint32_t)(i % m.nlines);
+    const uint32_t o  = o0 + ol;
+    double* lv   = list_val + ((size_t)o * m.nlines + l) * cap;
+    uint32_t* ln = list_nr + ((size_t)o * m.nlines + l) * cap;
+    uint32_t cnt = 0;
+    auto add = [&](uint32_t nr_new, double Ls_new) {
+        for (uint32_t k = 0; k < cnt; k++)
+            if (ln[k] == nr_new) { lv[k] += Ls_new; return; }
+        if (cnt >= cap) { atomicAdd(overflow, 1ull); return; }
+        lv[cnt] = Ls_new; ln[cnt] = nr_new; cnt++;
+    };
+    for (uint32_t rr = 0; rr < m.hnrays; rr++) {
+        const uint32_t ar = __ldg(&m.antipod[rr]);
+        if (lens[(size_t)o * m.nrays + rr] + lens[(size_t)o * m.nrays + ar] == 0) continue;
+        for (uint32_t z = 0; z < m.nquads; z++) {
+            const size_t idx = ((size_t)rr * no + ol) * m.nfreqs + (size_t)l * m.nquads + z;
+            add(o, L[idx]);
+            for (uint32_t mm = 0; mm < K; mm++)
+                for (uint32_t s = 0; s < 2; s++) {
+                    const uint32_t p = offN[(idx * K + mm) * 2 + s];
+                    if (p != 0xffffffffu) add(p, offV[(idx * K + mm) * 2 + s]);
+                }
+        }
+    }
+    for (uint32_t k = cnt; k < cap; k++) { lv[k] = 0.0; ln[k] = 0xffffffffu; }
+    lam_val[(size_t)o * m.nlines + l] = cnt ? lv[0] : 0.0; /* the diagonal element is always added first */
     lam_cnt[(size_t)o * m.nlines + l] = cnt;
 }
 

@@ -106,7 +106,7 @@ def test_errors_are_loud(ctx):
         c.npoints = 10
         c.run(2)
     with pytest.raises(cabi.MgbError):
-        c.set_params(n_off_diag=2)
+        c.set_params(n_off_diag=5)  # more than kMaxOffDiag = 4 off-diagonals
     c.close()
 
 
@@ -170,3 +170,31 @@ def test_ddiv_matches_ieee_division(ctx):
         want = A / B
     same = (got.view(np.uint64) == want.view(np.uint64)) | (np.isnan(got) & np.isnan(want))
     assert same.all(), f"{np.count_nonzero(~same)} mismatches, first: a={A[~same][:3]} b={B[~same][:3]} got={got[~same][:3]} want={want[~same][:3]}"
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_banded_lambda_against_reference(ctx, name):
+    """n_off_diag > 0: J and the (p, line) Lambda lists of the compiled reference (same points, same list lengths, values within
+    1e-10 after sorting each list by point), and the same against the oracle for the other ApproximationTypes."""
+    from magritte_b200.flatten import approx_of
+    from oracle import oracle as orc
+    flat, ref = util.load_golden_offdiag(name)
+    ctx.set_model(flat)
+    approx = approx_of(flat["params"])
+    ctx.run(approx)
+    assert util.relerr(ctx.get_J(), ref["J"]) <= TOL
+    val, nr, cnt = ctx.get_lambda_lists()
+    cap = ref["lambda_nr"].shape[2]
+    assert (nr[:, :, cap:] == 0xffffffff).all()
+    util.lambda_lists_close(val[:, :, :cap], nr[:, :, :cap], cnt, ref, TOL)
+    dval, dcnt = ctx.get_lambda()
+    assert np.array_equal(dcnt, cnt) and np.array_equal(dval, val[:, :, 0])
+    for other in (0, 1):
+        o = orc.Oracle(flat, approx=other, store_u=False)
+        o.solve()
+        ctx.run(other)
+        v2, n2, c2 = ctx.get_lambda_lists()
+        k = o.L_nr.shape[2]
+        want = dict(lambda_val=o.L_val, lambda_nr=o.L_nr, lambda_cnt=o.L_cnt)
+        util.lambda_lists_close(v2[:, :, :k], n2[:, :, :k], c2, want, TOL)
+    ctx.set_params(n_off_diag=0)
