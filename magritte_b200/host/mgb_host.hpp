@@ -571,6 +571,10 @@ class Model {
     }
     // ---- Model::compute_radiation_field_feautrier_order_2 (model.cpp:353-390) -> the C ABI ----
     int compute_radiation_field_feautrier_order_2() {
+        if (parameters.n_off_diag)
+            throw std::runtime_error("magritte_b200.core: n_off_diag > 0 couples the rate equations of neighbouring points (one global sparse system, "
+                                     "lineProducingSpecies.tpp:377-581); the host layer solves the block-diagonal case only. The banded Lambda "
+                                     "lists are available from the C ABI (mgb_get_lambda_lists).");
         sync_static(true);
         const Size L = nlines();
         J.resize((size_t)npoints * nfreqs);
