@@ -239,9 +239,9 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             const double B   = Bm + Cb;
             const uint2 pX   = *reinterpret_cast<const uint2*>(&MGB_REC(x, R_PTS));
             const double Ib  = boundary_intensity(m, pX.x, freq * shX);
-            st.a  = ddiv(S0 + 2.0 * Ib * inv, B);
+            const double Su0 = ddiv(S0 + 2.0 * Ib * inv, B);
             st.F  = 0.5 * Bm * dtau * dtau;
-            st.FI = drcp(1.0 + st.F);
+            st.a  = Su0 * (1.0 + st.F); /* the sweep carries b = Su * (1 + F): one reciprocal per row instead of two */
         } else {
             // interior row (solver.tpp:2264-2281; mirrored 2306-2311): the row's source is the line-integrated one of the
             // segment in which X is `curr` (the near segment on side 0, the far one on side 1)
@@ -249,10 +249,9 @@ __device__ __forceinline__ void sweep_step(const DevModel& m, const LaneLine& L,
             const double avg     = 0.5 * (st.dtau_far + dtau);
             const double invFar  = avg * st.dtau_far;
             const double invNear = avg * dtau;
-            const double Afar    = drcp(invFar);
-            st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-            st.FI = drcp(1.0 + st.F);
-            st.a  = (Afar * st.a + Sx) * st.FI * invNear;
+            const double P       = drcp(invFar * (1.0 + st.F)); /* A * FI of the previous row */
+            st.a  = (st.a * P + Sx) * invNear;
+            st.F  = (st.F * P + 1.0) * invNear;
         }
         st.dtau_far  = dtau;
         st.large_far = large;
@@ -341,10 +340,9 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const double avg     = 0.5 * (st.dtau_far + dtau);
     const double invFar  = avg * st.dtau_far;
     const double invNear = avg * dtau;
-    const double Afar    = drcp_inl(invFar);
-    st.F  = (Afar * st.F * st.FI + 1.0) * invNear;
-    st.FI = drcp_inl(1.0 + st.F);
-    st.a  = (Afar * st.a + Sx) * st.FI * invNear;
+    const double P       = drcp_inl(invFar * (1.0 + st.F)); /* A * FI of the previous row */
+    st.a  = (st.a * P + Sx) * invNear;
+    st.F  = (st.F * P + 1.0) * invNear;
     st.dtau_far  = dtau;
     st.large_far = large;
     st.SatY_far  = S_atY;
@@ -621,7 +619,7 @@ __global__ void __launch_bounds__(128, OFFD ? 2 : 4) k_solve(const __grid_consta
                     }
                     if (OFFD && part && hadX) { /* the row of X = q[-1] has just been eliminated */
                         const uint2 pX = *reinterpret_cast<const uint2*>(&MGB_REC(q - 1, R_PTS));
-                        hist[OFFD ? side : 0].push(st.F, st.FI, st.dtau_far, pX.x, MGB_REC(q - 1, R_SHIFT));
+                        hist[OFFD ? side : 0].push(st.F, drcp(1.0 + st.F), st.dtau_far, pX.x, MGB_REC(q - 1, R_SHIFT));
                     }
                 }
             }
@@ -629,6 +627,8 @@ __global__ void __launch_bounds__(128, OFFD ? 2 : 4) k_solve(const __grid_consta
             if (centre) break;
         }
         SC = st.SX; /* source function at the origin */
+        st.FI = drcp(1.0 + st.F); /* FI and Su of the row next to the origin, from the carried b = Su * (1 + F) */
+        st.a  = st.a * st.FI;
         nlarge += st.nlarge;
         if (side == 0) {
             double* s0 = ws.side0(lane);
