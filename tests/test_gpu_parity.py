@@ -163,8 +163,17 @@ def test_ddiv_matches_ieee_division(ctx):
     nr = 1 << 22
     b5 = np.concatenate([(sign(nr) | expo(nr, 0, 2047) | mant(nr)).view(np.float64), np.exp(rng.uniform(-140, 140, nr)), special,
                          np.ldexp(1.0 + rng.integers(0, 4, 4096) * 2.0 ** -52, rng.integers(-1022, 1024, 4096))])
-    A = np.concatenate([a, a2, a3, a4, np.ones(1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), np.ones(b5.size)])
-    B = np.concatenate([b, b2, b3, b4, rng.uniform(1, 2, 1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), b5])
+    # hard-to-round reciprocals: b = rn(1 / midpoint between two adjacent doubles) and its neighbours, mantissas of all ones / near 1
+    nh = 1 << 21
+    q = (rng.integers(1 << 52, 1 << 53, nh, dtype=np.uint64)).astype(np.longdouble)
+    mid = (2 * q + 1) / np.longdouble(2.0) ** 54                      # exact in 64-bit-mantissa long double
+    bh = (np.longdouble(1.0) / mid).astype(np.float64)
+    bh = np.concatenate([bh, np.nextafter(bh, 0.0), np.nextafter(bh, 4.0)]) * np.ldexp(1.0, rng.integers(-60, 60, 3 * nh))
+    ones_m = ((np.uint64(1) << np.uint64(52)) - rng.integers(1, 64, 4096, dtype=np.uint64)) | expo(4096, 900, 1100)
+    near1 = rng.integers(0, 64, 4096, dtype=np.uint64) | expo(4096, 900, 1100)
+    b6 = np.concatenate([bh, ones_m.view(np.float64), near1.view(np.float64)])
+    A = np.concatenate([a, a2, a3, a4, np.ones(1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), np.ones(b5.size), np.ones(b6.size)])
+    B = np.concatenate([b, b2, b3, b4, rng.uniform(1, 2, 1000), rng.integers(1, 1 << 20, 1000).astype(np.float64), b5, b6])
     got = ctx.ddiv(A, B)
     with np.errstate(all="ignore"):
         want = A / B
