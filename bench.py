@@ -417,6 +417,8 @@ def run_b200(args):
 
 
 def main():
+    # rank 0 prints exactly ONE line on stdout: NCCL's own version/debug lines (NCCL_DEBUG=VERSION/INFO on some boxes) go to stderr
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
     args = parse()
     if args.impl == "reference":
         run_reference(args)
