@@ -119,8 +119,10 @@ def algorithmic_flops(flat, n_entries, n_solves):
     return 54 * int(flat["nquads"]) * n_entries + 110 * n_solves
 
 
-def cpu_baseline_port(flat, seconds, approx):
-    """The oracle (CPU restatement of the reference's algorithm, OpenMP over origins) on a bounded origin sample."""
+def cpu_baseline_port(flat, seconds, approx, J_gpu=None):
+    """The oracle (CPU restatement of the reference's algorithm, OpenMP over origins) on a bounded origin sample. With J_gpu (the
+    full-size J of the CUDA path) the sample doubles as a full-size parity check: the oracle's rows, in the reference's elimination
+    order, against the same rows of the GPU result."""
     from oracle import oracle as orc
     cores = os.cpu_count() or 1
     o = orc.Oracle(flat, approx=approx, store_u=False, threads=cores)
@@ -139,9 +141,14 @@ def cpu_baseline_port(flat, seconds, approx):
     o.solve(o_range=(start, start + no), rr_range=(0, H), half_length=hl)
     dt = time.perf_counter() - t0
     solves = no * H * F
-    return {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
-            "sample": f"{no} consecutive origins (from {start}) x all {H} ray pairs x {F} freqs = {solves} solves in {dt:.2f} s, "
-                      f"oracle/feautrier_oracle.c with OpenMP"}
+    res = {"value": solves / dt, "unit": "solves/s", "cores": cores, "kind": "port",
+           "sample": f"{no} consecutive origins (from {start}) x all {H} ray pairs x {F} freqs = {solves} solves in {dt:.2f} s, "
+                     f"oracle/feautrier_oracle.c with OpenMP"}
+    if J_gpu is not None:
+        a, b = np.asarray(J_gpu[start:start + no]), o.J[start:start + no]
+        res["parity_vs_gpu"] = {"origins": no, "max_rel_err_J": float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1e-300))),
+                                "tolerance": 1e-10, "note": "full-size workload: oracle rows (reference elimination order) vs the CUDA result"}
+    return res
 
 
 def run_reference(args):
@@ -379,7 +386,9 @@ def run_b200(args):
                                 "note": "ray paths kept in HBM across calls (static geometry), as inside an ALI loop"},
                "s_per_levelpop_iter": None}
         if not args.no_cpu_baseline and world == 1:
-            out["cpu_baseline"] = cpu_baseline_port(flat, args.cpu_seconds, approx)
+            out["cpu_baseline"] = cpu_baseline_port(flat, args.cpu_seconds, approx, J_gpu=h_J)
+            if out["cpu_baseline"]["parity_vs_gpu"]["max_rel_err_J"] > 1e-10:
+                raise SystemExit(f"bench.py: full-size parity check failed: {out['cpu_baseline']['parity_vs_gpu']}")
         elif world == 1:
             out["cpu_baseline"] = None
     # ---------------- imaging leg (BASELINE.json configs[4] shape on this model): pixels partitioned over the ranks ----------------

@@ -388,3 +388,45 @@ def spec_wind_3d(npoints=100000, nside_rays=4, nquads=11, nside_shell=None, seed
 
 def build(core, io, name, spec):
     return assemble(core, io, name, **spec)
+
+
+def spec_lattice_sphere(npoints=10_000_000, nside_rays=1, nquads=3, seed=1234, line_keep=(1,), v_inf=15.0e3):
+    """BASELINE configs[4] (SURVEY 8d "C5 inputs"): a point cloud of ~npoints points on a jittered cubic lattice masked to a
+    sphere of radius 1e14 m (spacing a, jitter U(-0.3a, 0.3a)), 26-stencil neighbour lists built in O(N) with numpy (Qhull at
+    10M points is not practical), boundary = lattice points with a stencil neighbour outside the sphere, the radial laws of
+    spec_wind_3d (radii below r_in = 1e12 m are clamped to r_in in the laws), CO restricted to one transition (J = 2-1)."""
+    rng = np.random.default_rng(seed)
+    r_in, r_out = 1.0e12, 1.0e14
+    n = int(round((npoints * 6.0 / math.pi) ** (1.0 / 3.0)))          # (pi/6) n^3 lattice points inside the sphere
+    a = 2.0 * r_out / n
+    idx = np.arange(n, dtype=np.float64) - (n - 1) / 2.0
+    inside = (idx[:, None, None] ** 2 + idx[None, :, None] ** 2 + idx[None, None, :] ** 2) <= (n / 2.0) ** 2
+    ids = np.full((n + 2, n + 2, n + 2), -1, dtype=np.int64)               # one layer of padding: no wrap-around
+    N = int(inside.sum())
+    core = ids[1:-1, 1:-1, 1:-1]
+    core[inside] = np.arange(N, dtype=np.int64)
+    ii, jj, kk = np.nonzero(inside)
+    position = (np.stack([idx[ii], idx[jj], idx[kk]], axis=1) + rng.uniform(-0.3, 0.3, (N, 3))) * a
+    offs = [(dx, dy, dz) for dx in (-1, 0, 1) for dy in (-1, 0, 1) for dz in (-1, 0, 1) if (dx, dy, dz) != (0, 0, 0)]
+    cols = np.empty((N, 26), dtype=np.int64)
+    for c, (dx, dy, dz) in enumerate(offs):
+        cols[:, c] = ids[ii + 1 + dx, jj + 1 + dy, kk + 1 + dz]
+    valid = cols >= 0
+    n_nbs = valid.sum(axis=1).astype(np.uint32)
+    nbs = cols[valid].astype(np.uint32)                                   # row-major: the lists in stencil order
+    boundary2point = np.nonzero(n_nbs < 26)[0].astype(np.uint32)
+    del cols, valid, ids
+    rr = np.maximum(np.linalg.norm(position, axis=1), r_in)
+    rhat = position / np.maximum(np.linalg.norm(position, axis=1), 1e-300)[:, None]
+    vel = (v_inf * (1.0 - 0.9 * r_in / rr) / CC)[:, None] * rhat
+    nH2 = 1.0e16 * (r_in / rr) ** 2
+    temperature = 2500.0 * (r_in / rr) ** 0.6 + 10.0
+    vturb2 = (1.5e3 / CC) ** 2 * np.ones(N)
+    direction = antipodal_ray_set(nside_rays)
+    weight = np.full(direction.shape[0], 1.0 / direction.shape[0])
+    ld = restrict_lines(load_species("co"), line_keep)
+    symbols = [ld["sym"], "H2", "e-"]
+    abundance = np.stack([1.0e-4 * nH2, nH2, np.zeros(N)], axis=1)
+    return dict(dimension=3, spherical=False, position=position, velocity=vel, nbs=nbs, n_nbs=n_nbs, boundary2point=boundary2point,
+                direction=direction, weight=weight, symbols=symbols, abundance=abundance, temperature=temperature, vturb2=vturb2,
+                linedata=[ld], nquads=nquads)
