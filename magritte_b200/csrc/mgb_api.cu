@@ -398,11 +398,11 @@ int fill_chunk(mgb_ctx* ctx, PathChunk& ch, mgb_stats* st, uint32_t& launches) {
 template <int APPROX, bool OFFD>
 cudaError_t launch_solve2(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
     const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
-    const size_t blocks = (nitems * 32 + 127) / 128;
-    const size_t smem   = 4 * solve_smem_per_warp(ctx->lines_per_warp);
+    const size_t blocks = (nitems + kSolveWarps - 1) / kSolveWarps;
+    const size_t smem   = kSolveWarps * solve_smem_per_warp(ctx->lines_per_warp);
     cudaError_t e = cudaFuncSetAttribute(k_solve<APPROX, OFFD>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    k_solve<APPROX, OFFD><<<(unsigned)blocks, 128, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
+    k_solve<APPROX, OFFD><<<(unsigned)blocks, 32 * kSolveWarps, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
                                                                         ctx->lines_per_warp);
     return cudaGetLastError();
 }

@@ -18,6 +18,7 @@ namespace {
 __global__ void k_trace_dump(DevModel m, uint32_t o, uint32_t r, uint32_t l, uint32_t cap, uint32_t* nr, uint32_t* nri, double* fac,
                              double* sh, double* dz, uint32_t* n_out) {
     const unsigned lane = threadIdx.x & 31;
+    stage_exp_table();
     const RayFrame fr   = make_frame(m, o, r);
     double Z = 0.0, dZ = 0.0;
     uint32_t ns, n_emit = 0;
@@ -63,6 +64,7 @@ __global__ void k_trace_dump(DevModel m, uint32_t o, uint32_t r, uint32_t l, uin
 
 __global__ void k_libm(int fn, unsigned long long n, const float* x, const float* y, float* out) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+    stage_exp_table();
     if (i >= n) return;
     float r;
     switch (fn) {

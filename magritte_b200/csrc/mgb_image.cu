@@ -238,6 +238,7 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
                                                      const double* __restrict__ shift0, ImagePaths ip, double* __restrict__ I) {
     const unsigned lane = threadIdx.x & 31;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    stage_exp_table();
     if (item >= (size_t)npix * nchunks_f) return;
     const uint32_t pix = (uint32_t)(item / nchunks_f), cf = (uint32_t)(item % nchunks_f);
     const uint32_t f0  = cf * 32 + lane;

@@ -59,6 +59,9 @@ MGB_LIBM_TAB uint64_t mgb_exp2f_tab[32] = {
     0x3feee89f995ad3adull, 0x3feeff76f2fb5e47ull, 0x3fef199bdd85529cull, 0x3fef3720dcef9069ull,
     0x3fef5818dcfba487ull, 0x3fef7c97337b9b5full, 0x3fefa4afa2a490daull, 0x3fefd0765b6e4540ull};
 
+#ifndef MGB_EXP2F_TAB /* where the 2^(i/32) table is read from (a device build may stage it in shared memory) */
+#define MGB_EXP2F_TAB(i) mgb_exp2f_tab[i]
+#endif
 // expf used inside erff: device code may route it to a shared out-of-line instance (mgb_device.cuh)
 #ifndef MGB_ERFF_EXPF
 #define MGB_ERFF_EXPF mgb_expf
@@ -84,7 +87,7 @@ MGB_LIBM_TAB double mgb_powf_log2c[16] = {
 // 2^(k/32) * (1 + C2' r + C1' r^2 + C0' r^3) core shared by expf (coefficients pre-scaled by 1/32^i)
 // and powf (unscaled); `ki` carries k in its low bits (the "shift" trick), sign_bias goes to bit 63.
 MGB_LIBM_FN float mgb_exp2f_core(double r, uint64_t ki, uint64_t sign_bias, double C0, double C1, double C2) {
-    uint64_t t = mgb_exp2f_tab[ki & 31];
+    uint64_t t = MGB_EXP2F_TAB(ki & 31);
     t += (ki + sign_bias) << 47;
     const double s  = MGB_LL2D((int64_t)t);
     const double z  = MGB_FMA(r, C0, C1);

@@ -528,12 +528,22 @@ struct SideHistory {
     __device__ __forceinline__ unsigned slot(unsigned j) const { return (cnt - 1u - j) % R; } // j-th nearest to the origin
 };
 
+// CTA shape of k_solve: kSolveWarps warps, kSolveCtas CTAs per SM (register cap 65536 / (32 * warps * ctas))
+#ifndef MGB_SOLVE_WARPS
+#define MGB_SOLVE_WARPS 4
+#endif
+#ifndef MGB_SOLVE_CTAS
+#define MGB_SOLVE_CTAS 4
+#endif
+constexpr int kSolveWarps = MGB_SOLVE_WARPS, kSolveCtas = MGB_SOLVE_CTAS;
+
 template <int APPROX, bool OFFD>
-__global__ void __launch_bounds__(128, OFFD ? 2 : 4) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
+__global__ void __launch_bounds__(32 * kSolveWarps, OFFD ? 2 : kSolveCtas) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
                                                   const FreqChunk* __restrict__ chunks, uint32_t nchunks_f, uint32_t lpw) {
     const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const size_t nitems = (size_t)pv.no * m.hnrays * nchunks_f;
+    stage_exp_table();
     if (item >= nitems) return; /* whole warps only */
     WarpSmem ws;
     ws.lpw  = lpw;
