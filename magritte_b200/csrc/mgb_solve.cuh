@@ -309,16 +309,14 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     if (!__all_sync(0xffffffffu, ok)) return false;
     if (!part) return true;
     const double dzX = MGB_REC(x, R_DZ);
-    double chiY, SY;
+    double chiY, eta = 0.0; /* an empty window: S = 0 / min_opacity */
     if (clsY == WIN_OWN) {
         const double prof = gaussian(MGB_REC(q, R_IW), frY - L.s_own);
-        const double eta  = 0.0 + prof * MGB_REC(q, R_IE);
+        eta = 0.0 + prof * MGB_REC(q, R_IE);
         if (APPROX == APPROX_ONELINE) chiY = (0.0 + prof * MGB_REC(q, R_IO)) + m.min_opacity;
         else chiY = m.min_opacity + prof * MGB_REC(q, R_IO);
-        SY = ddiv(eta, chiY);
     } else {
         chiY = m.min_opacity;
-        SY   = zero_over(chiY);
     }
     double dtau, S_atX = 0.0, S_atY = 0.0;
     if (large) {
@@ -340,7 +338,8 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const double avg     = 0.5 * (st.dtau_far + dtau);
     const double invFar  = avg * st.dtau_far;
     const double invNear = avg * dtau;
-    const double P       = drcp_inl(invFar * (1.0 + st.F)); /* A * FI of the previous row */
+    const DivRcp dr      = ddiv_drcp(eta, chiY, invFar * (1.0 + st.F)); /* S at Y; A * FI of the previous row */
+    const double SY = dr.q, P = dr.r;
     st.a  = (st.a * P + Sx) * invNear;
     st.F  = (st.F * P + 1.0) * invNear;
     st.dtau_far  = dtau;
