@@ -79,7 +79,15 @@ __global__ void k_libm(int fn, unsigned long long n, const float* x, const float
 
 __global__ void k_ddiv(unsigned long long n, const double* a, const double* b, double* out) {
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) out[i] = (a[i] == 1.0 && !signbit(a[i])) ? drcp(b[i]) : ddiv(a[i], b[i]); /* 1/b call sites use drcp */
+    if (i >= n) return;
+    out[i] = (a[i] == 1.0 && !signbit(a[i])) ? drcp(b[i]) : ddiv(a[i], b[i]); /* 1/b call sites use drcp */
+    /* ddiv2 (two numerators, one reciprocal refinement) must give ddiv's bits for both; a mismatch poisons the output */
+    const unsigned long long j = (i ^ 1ull) < n ? (i ^ 1ull) : i;
+    const Div2 d = ddiv2(a[i], a[j], b[i]);
+    const double w1 = ddiv(a[i], b[i]), w2 = ddiv(a[j], b[i]);
+    const bool same1 = __double_as_longlong(d.q1) == __double_as_longlong(w1) || (d.q1 != d.q1 && w1 != w1);
+    const bool same2 = __double_as_longlong(d.q2) == __double_as_longlong(w2) || (d.q2 != d.q2 && w2 != w2);
+    if (!(same1 && same2)) out[i] = __longlong_as_double(0x4242424242424242ll);
 }
 
 // 8 independent DFMA chains per thread; explicit fma() because the file is compiled with -fmad=false.

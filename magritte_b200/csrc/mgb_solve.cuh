@@ -142,7 +142,8 @@ __device__ __noinline__ LineIntegral line_integrated_own(double min_opacity, dou
     double d = sum_dtau;
     const double bound_min_dtau = min_opacity * dz;
     if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
-    dtau = d; S_atX = ddiv(sum_x, d); S_atY = ddiv(sum_y, d);
+    const Div2 dv = ddiv2(sum_x, sum_y, d); /* one reciprocal refinement for both ends */
+    dtau = d; S_atX = dv.q1; S_atY = dv.q2;
     return LineIntegral{dtau, S_atX, S_atY};
 }
 
@@ -309,14 +310,16 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     if (!__all_sync(0xffffffffu, ok)) return false;
     if (!part) return true;
     const double dzX = MGB_REC(x, R_DZ);
-    double chiY, eta = 0.0; /* an empty window: S = 0 / min_opacity */
+    double chiY, SY;
     if (clsY == WIN_OWN) {
         const double prof = gaussian(MGB_REC(q, R_IW), frY - L.s_own);
-        eta = 0.0 + prof * MGB_REC(q, R_IE);
+        const double eta  = 0.0 + prof * MGB_REC(q, R_IE);
         if (APPROX == APPROX_ONELINE) chiY = (0.0 + prof * MGB_REC(q, R_IO)) + m.min_opacity;
         else chiY = m.min_opacity + prof * MGB_REC(q, R_IO);
+        SY = ddiv(eta, chiY);
     } else {
         chiY = m.min_opacity;
+        SY   = zero_over(chiY);
     }
     double dtau, S_atX = 0.0, S_atY = 0.0;
     if (large) {
@@ -338,8 +341,7 @@ __device__ __forceinline__ bool sweep_step_common(const DevModel& m, const LaneL
     const double avg     = 0.5 * (st.dtau_far + dtau);
     const double invFar  = avg * st.dtau_far;
     const double invNear = avg * dtau;
-    const DivRcp dr      = ddiv_drcp(eta, chiY, invFar * (1.0 + st.F)); /* S at Y; A * FI of the previous row */
-    const double SY = dr.q, P = dr.r;
+    const double P       = drcp_inl(invFar * (1.0 + st.F)); /* A * FI of the previous row */
     st.a  = (st.a * P + Sx) * invNear;
     st.F  = (st.F * P + 1.0) * invNear;
     st.dtau_far  = dtau;

@@ -141,7 +141,8 @@ def test_device_libm_bit_exact(ctx, fn):
 def test_ddiv_matches_ieee_division(ctx):
     """The kernels' scaled division (mgb_device.cuh: ddiv) must equal IEEE-754 round-to-nearest a/b bit for bit:
     16M random operand pairs over the whole exponent range (incl. the 1e-30..1e-60 magnitudes of SI emissivities),
-    pairs with nearly equal mantissas, exact quotients, zeros, subnormals, inf and NaN."""
+    pairs with nearly equal mantissas, exact quotients, zeros, subnormals, inf and NaN. The self-test kernel also runs ddiv2
+    (a[i] / b[i] and a[i^1] / b[i] with one reciprocal refinement) and poisons the output where its bits differ from ddiv's."""
     rng = np.random.default_rng(11)
     n = 1 << 24
     mant = lambda k: rng.integers(0, 1 << 52, k, dtype=np.uint64)
