@@ -122,6 +122,11 @@ int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32
  * length (0 or 1). u: radiation.u rows, [hnrays][(o_end-o_begin)][nfreqs], only if store_intensities. */
 int mgb_get_J(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J);
 int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* lambda_val, uint32_t* lambda_cnt);
+/* The memory-sparse solver's output (Solver::solve_feautrier_order_2_sparse, solver.tpp:297-363; what
+ * Model::compute_radiation_field_feautrier_order_2_sparse leaves in lspec.J): J integrated over each line's quadrature,
+ * J_lines [(o_end-o_begin)][nlines] (line = global line index; species s owns columns nrad_cum[s] .. +nrad[s]). Every run
+ * accumulates it next to J from the same solves, in the reference's rr > line > z order. */
+int mgb_get_J_lines(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J_lines);
 int mgb_get_u(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* u);
 /* n_off_diag = K > 0 (banded approximate Lambda operator, Solver::update_Lambda solver.tpp:1806-1850 with L_lower/L_upper of
  * :2320-2355): the (p, line) lists of Lambda::add_element (lambda.tpp:79-89) in the reference's insertion order.

@@ -516,6 +516,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     const size_t prow = (size_t)((m.npoints + ctx->nranks - 1) / ctx->nranks) * ctx->nranks;
     MGB_CUDA(ctx, ctx->J.ensure(8 * prow * m.nfreqs));
     MGB_CUDA(ctx, ctx->lam_val.ensure(8 * prow * m.nlines));
+    MGB_CUDA(ctx, ctx->J_lines.ensure(8 * prow * m.nlines));
     MGB_CUDA(ctx, ctx->lam_cnt.ensure(4 * prow * m.nlines));
     double* u_full = nullptr;
     if (ctx->params.store_intensities) {
@@ -562,6 +563,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         tr.start();
         const size_t nj = (size_t)no * m.nfreqs, nl = (size_t)no * m.nlines;
         k_reduce_J<<<(unsigned)((nj + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J.as<double>(), u_full, ctx->u_o0, ctx->u_no);
+        k_reduce_J_lines<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_lines.as<double>());
         if (K)
             k_reduce_lambda_banded<<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(
                 m, ch->o0, no, K, ctx->lam_cap, ctx->lens.as<uint32_t>(), sc.L, sc.offV, sc.offN, ctx->lam_list_val.as<double>(),
@@ -571,7 +573,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
                                                                                    ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
         MGB_CUDA(ctx, cudaGetLastError());
         st.ms_reduce += tr.stop();
-        launches += 2;
+        launches += 3;
     }
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     st.ms_total = total.stop();
@@ -605,6 +607,15 @@ extern "C" int mgb_get_J(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double*
     cudaSetDevice(ctx->device);
     const size_t F = ctx->m.nfreqs;
     MGB_CUDA(ctx, cudaMemcpy(J, ctx->J.as<double>() + (size_t)o_begin * F, 8 * (size_t)(o_end - o_begin) * F, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_J_lines(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J_lines) {
+    if (!ctx || !J_lines) return MGB_EINVAL;
+    MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_J_lines"));
+    cudaSetDevice(ctx->device);
+    const size_t L = ctx->m.nlines;
+    MGB_CUDA(ctx, cudaMemcpy(J_lines, ctx->J_lines.as<double>() + (size_t)o_begin * L, 8 * (size_t)(o_end - o_begin) * L, cudaMemcpyDeviceToHost));
     return MGB_OK;
 }
 

@@ -99,13 +99,14 @@ extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
     ncclComm_t comm = (ncclComm_t)ctx->comm;
     // all-gather with per-rank row counts, in place: every rank's slice already sits at its global rows, one broadcast per owner
     ncclResult_t r = g_nccl.GroupStart();
-    char* J = (char*)ctx->J.p; char* lv = (char*)ctx->lam_val.p; char* lc = (char*)ctx->lam_cnt.p;
+    char* J = (char*)ctx->J.p; char* lv = (char*)ctx->lam_val.p; char* lc = (char*)ctx->lam_cnt.p; char* jl = (char*)ctx->J_lines.p;
     for (int root = 0; root < ctx->nranks && !r; root++) {
         const size_t o0 = ctx->part_bounds[root], rows = ctx->part_bounds[root + 1] - o0;
         if (!rows) continue;
         const size_t nJ = rows * m.nfreqs, nL = rows * m.nlines;
         r = g_nccl.Broadcast(J + 8 * o0 * m.nfreqs, J + 8 * o0 * m.nfreqs, nJ, ncclFloat64, root, comm, ctx->stream);
         if (!r) r = g_nccl.Broadcast(lv + 8 * o0 * m.nlines, lv + 8 * o0 * m.nlines, nL, ncclFloat64, root, comm, ctx->stream);
+        if (!r) r = g_nccl.Broadcast(jl + 8 * o0 * m.nlines, jl + 8 * o0 * m.nlines, nL, ncclFloat64, root, comm, ctx->stream);
         if (!r) r = g_nccl.Broadcast(lc + 4 * o0 * m.nlines, lc + 4 * o0 * m.nlines, nL, ncclUint32, root, comm, ctx->stream);
     }
     const ncclResult_t r2 = g_nccl.GroupEnd();

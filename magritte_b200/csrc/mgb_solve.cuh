@@ -43,7 +43,7 @@ struct FreqChunk {
 
 // Record buffer of one line: kRecFields rows of kRecStride doubles. Slot 0 carries the last record of the
 // previous round (the far end X of the first segment of this round), slots 1..32 hold this round's entries.
-constexpr int kRecStride = 34;       // 33 slots + 1 pad (distinct banks per line)
+constexpr int kRecStride = 33;       // 33 slots; odd stride, and consecutive lines start 20 banks apart
 constexpr int kRecFields = 10;
 enum { R_SHIFT = 0, R_DZ, R_IW, R_IE, R_IO, R_SLINE, R_DSM, R_SQW, R_FACTOR, R_PTS /* uint2 {nr, nr_interp} */ };
 #define MGB_REC(q, fld) ((q)[(fld) * kRecStride])
@@ -529,17 +529,19 @@ struct SideHistory {
     __device__ __forceinline__ unsigned slot(unsigned j) const { return (cnt - 1u - j) % R; } // j-th nearest to the origin
 };
 
-// CTA shape of k_solve: kSolveWarps warps, kSolveCtas CTAs per SM (register cap 65536 / (32 * warps * ctas))
+// CTA shape of k_solve: kSolveWarps warps, kSolveCtas CTAs per SM (register cap 65536 / (32 * warps * ctas)). Work items differ a lot
+// in length and a CTA keeps its shared memory until its slowest warp is done: 8 CTAs of 2 warps beat 4 of 4 by 1.6 % (16 warps per SM
+// either way; 8 x (2 x 13760 B + 256 B table + 1 KB reserved) just fits the 228 KB of an SM, which is why the record stride is 33).
 #ifndef MGB_SOLVE_WARPS
-#define MGB_SOLVE_WARPS 4
+#define MGB_SOLVE_WARPS 2
 #endif
 #ifndef MGB_SOLVE_CTAS
-#define MGB_SOLVE_CTAS 4
+#define MGB_SOLVE_CTAS 8
 #endif
 constexpr int kSolveWarps = MGB_SOLVE_WARPS, kSolveCtas = MGB_SOLVE_CTAS;
 
 template <int APPROX, bool OFFD>
-__global__ void __launch_bounds__(32 * kSolveWarps, OFFD ? 2 : kSolveCtas) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
+__global__ void __launch_bounds__(32 * kSolveWarps, OFFD ? kSolveCtas / 2 : kSolveCtas) k_solve(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, ScratchView sc,
                                                   const FreqChunk* __restrict__ chunks, uint32_t nchunks_f, uint32_t lpw) {
     const unsigned lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -815,6 +817,22 @@ __global__ void k_reduce_J(DevModel m, uint32_t o0, uint32_t no, const double* _
         if (u_full) u_full[((size_t)rr * u_no + (o0 + ol - u_o0)) * m.nfreqs + f] = v;
     }
     J[(size_t)(o0 + ol) * m.nfreqs + f] = acc;
+}
+
+// The memory-sparse solver's accumulator (Solver::solve_feautrier_order_2_sparse, solver.tpp:297-363): J(o, line) integrated over the
+// line's quadrature, lspec.J(o,k) += quadrature.weights[z] * wt * Su[centre] in the loop nest rr > k > z, wt = 2 * weight(rr); the
+// boundary intensity stands in for an isolated origin (scratch u holds it).
+__global__ void k_reduce_J_lines(DevModel m, uint32_t o0, uint32_t no, const double* __restrict__ u, double* __restrict__ J_lines) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)no * m.nlines) return;
+    const uint32_t ol = (uint32_t)(i / m.nlines), l = (uint32_t)(i % m.nlines);
+    double acc = 0.0;
+    for (uint32_t rr = 0; rr < m.hnrays; rr++) {
+        const double wt = __ldg(&m.weight[rr]) * 2.0;
+        for (uint32_t z = 0; z < m.nquads; z++)
+            acc += __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * wt * u[((size_t)rr * no + ol) * m.nfreqs + (size_t)l * m.nquads + z];
+    }
+    J_lines[(size_t)(o0 + ol) * m.nlines + l] = acc;
 }
 
 // Lambda(o, lid) = sum over rr, then z, of the increments, in the order Lambda::add_element saw them
