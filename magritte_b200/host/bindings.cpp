@@ -104,6 +104,10 @@ PYBIND11_MODULE(core, m) {
         .def("compute_Jeff", &Model::compute_Jeff)
         .def("compute_level_populations_from_stateq", &Model::compute_level_populations_from_stateq)
         .def("compute_level_populations", &Model::compute_level_populations)
+        .def("compute_radiation_field_feautrier_order_2_sparse", &Model::compute_radiation_field_feautrier_order_2_sparse)
+        .def("compute_Jeff_sparse", &Model::compute_Jeff_sparse)
+        .def("compute_level_populations_from_stateq_sparse", &Model::compute_level_populations_from_stateq_sparse)
+        .def("compute_level_populations_sparse", &Model::compute_level_populations_sparse)
         .def("compute_image_new", &Model::compute_image_new)
         // test hook: radiation.J and the diagonal Lambda lists as a radiation-field call leaves them (host-only tests of compute_Jeff / stateq)
         .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt) {
@@ -133,6 +137,7 @@ PYBIND11_MODULE(core, m) {
         })
         .def("get_population_tot", [](const Model& s, Size l) { const auto& v = s.lineProducingSpecies.at(l).population_tot; return py::array_t<double>(v.size(), v.data()); })
         .def("get_Jeff", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.Jeff, s.npoints, ls.linedata.nrad); })
+        .def("get_J_species", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.J, s.npoints, ls.linedata.nrad); })
         .def("get_Jlin", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.Jlin, s.npoints, ls.linedata.nrad); })
         .def("get_lambda", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l); return out2(ls.lambda_Ls, s.npoints, ls.linedata.nrad); })
         .def("convergence", [](const Model& s, Size l) { const auto& ls = s.lineProducingSpecies.at(l);

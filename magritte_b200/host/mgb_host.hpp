@@ -188,6 +188,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
     std::vector<Real> population_tot;
     std::vector<VecLD> populations, residuals;
     std::vector<Real> Jlin, Jeff, Jdif;      // [npoints][nrad]
+    std::vector<Real> J;                     // [npoints][nrad] line-integrated mean intensity of the memory-sparse solver (lspec.J)
     std::vector<Real> lambda_Ls;             // [npoints][nrad] the diagonal ALO element (nr == p), lambda.tpp:79-89
     std::vector<Size> lambda_cnt;            // [npoints][nrad] list length (0 or 1)
     Real fraction_not_converged = 0, relative_change_mean = 0, relative_change_max = 0;
@@ -200,7 +201,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         population.assign(n, 0); population_prev1.assign(n, 0); population_prev2.assign(n, 0); population_prev3.assign(n, 0);
         trial_population.assign(n, 0); trial_population_prev.assign(n, 0);
         population_tot.assign(np, 0);
-        Jlin.assign((size_t)np * linedata.nrad, 0); Jeff = Jlin; Jdif = Jlin; lambda_Ls = Jlin;
+        Jlin.assign((size_t)np * linedata.nrad, 0); Jeff = Jlin; Jdif = Jlin; lambda_Ls = Jlin; J = Jlin;
         lambda_cnt.assign((size_t)np * linedata.nrad, 0);
     }
     // lineProducingSpecies.tpp:23-44
@@ -322,7 +323,11 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         populations.pop_back();
     }
     // lineProducingSpecies.tpp:377-581, block by block (see the header comment). Needs Jeff and the diagonal Lambda element.
-    void update_using_statistical_equilibrium(const std::vector<Real>& abundance, const Size nspecs, const std::vector<Real>& temperature) {
+    // `sparse`: update_using_statistical_equilibrium_sparse (lineProducingSpecies.tpp:589-705), the same per-point matrix solved by a
+    // column-pivoted Householder QR as the reference does there.
+    void update_using_statistical_equilibrium(const std::vector<Real>& abundance, const Size nspecs, const std::vector<Real>& temperature,
+                                              const bool sparse = false) {
+        if (sparse && parameters->n_off_diag != 0) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update.");
         const Size nlev = linedata.nlev;
         population_prev3 = population_prev2; population_prev2 = population_prev1; population_prev1 = population;
         residuals.push_back(diff(population, populations.back()));
@@ -367,6 +372,11 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
                 }
                 for (Size i = 0; i < nlev; i++) add(nlev - 1, i, 1.0L);
                 y[nlev - 1] = population_tot[p];
+                if (sparse) {
+                    const VecLD x = colpiv_qr_solve(M, y, nlev);
+                    for (Size i = 0; i < nlev; i++) population[index(p, i)] = x[i];
+                    continue;
+                }
                 if (!lu_solve(M, y, nlev)) { failed = true; continue; }
                 for (Size i = 0; i < nlev; i++) population[index(p, i)] = y[i];
             }
@@ -595,6 +605,51 @@ class Model {
         }
         return 0;
     }
+    // ---- Model::compute_radiation_field_feautrier_order_2_sparse (model.cpp:474-510; Solver::solve_feautrier_order_2_sparse,
+    //      solver.tpp:297-363): the same solves, but only J integrated over each line (lspec.J) and Lambda leave the device ----
+    int compute_radiation_field_feautrier_order_2_sparse() {
+        if (parameters.n_off_diag) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update.");
+        sync_static(true);
+        const Size L = nlines();
+        std::vector<double> jl((size_t)npoints * L), lam((size_t)npoints * L);
+        std::vector<uint32_t> cnt((size_t)npoints * L);
+        std::vector<double> ptot((size_t)nlspecs() * npoints);
+        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
+        check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+        check(mgb_run_feautrier_order_2(ctx, approx(), 0, npoints, &last_stats), "mgb_run_feautrier_order_2");
+        check(mgb_get_J_lines(ctx, 0, npoints, jl.data()), "mgb_get_J_lines");
+        check(mgb_get_lambda(ctx, 0, npoints, lam.data(), cnt.data()), "mgb_get_lambda");
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& ls = lineProducingSpecies[l];
+            const Size nrad = ls.linedata.nrad;
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    ls.J[(size_t)p * nrad + k]          = jl[(size_t)p * L + nrad_cum[l] + k];
+                    ls.lambda_Ls[(size_t)p * nrad + k]  = lam[(size_t)p * L + nrad_cum[l] + k];
+                    ls.lambda_cnt[(size_t)p * nrad + k] = cnt[(size_t)p * L + nrad_cum[l] + k];
+                }
+        }
+        return 0;
+    }
+    // ---- Model::compute_Jeff_sparse (model.cpp:549-570) ----
+    int compute_Jeff_sparse() {
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& lspec = lineProducingSpecies[l];
+            const Size nrad = lspec.linedata.nrad;
+#pragma omp parallel for schedule(static)
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    double diff = 0.0;
+                    for (Size m = 0; m < lspec.lambda_cnt[(size_t)p * nrad + k]; m++) {
+                        const Size I = lspec.index(p, lspec.linedata.irad[k]);
+                        diff += lspec.lambda_Ls[(size_t)p * nrad + k] * lspec.population[I];
+                    }
+                    lspec.Jlin[(size_t)p * nrad + k] = lspec.J[(size_t)p * nrad + k];
+                    lspec.Jeff[(size_t)p * nrad + k] = lspec.Jlin[(size_t)p * nrad + k] - HH_OVER_FOUR_PI * diff;
+                }
+        }
+        return 0;
+    }
     // ---- Model::compute_Jeff (model.cpp:514-545) ----
     int compute_Jeff() {
         const Size nq = nquads();
@@ -622,6 +677,16 @@ class Model {
     int compute_level_populations_from_stateq() {
         for (auto& lspec : lineProducingSpecies) {
             lspec.update_using_statistical_equilibrium(abundance, nspecs, temperature_gas);
+            lspec.correct_negative_populations(temperature_gas);
+            lspec.check_for_convergence(parameters.pop_prec);
+        }
+        set_emissivity_and_opacity();
+        return 0;
+    }
+    // ---- Lines::iteration_using_statistical_equilibrium_sparse (lines.cpp:139-150) ----
+    int compute_level_populations_from_stateq_sparse() {
+        for (auto& lspec : lineProducingSpecies) {
+            lspec.update_using_statistical_equilibrium(abundance, nspecs, temperature_gas, true);
             lspec.correct_negative_populations(temperature_gas);
             lspec.check_for_convergence(parameters.pop_prec);
         }
@@ -662,7 +727,10 @@ class Model {
         return std::make_tuple(false, 0u);
     }
     // ---- Model::compute_level_populations (model.cpp:655-748) ----
-    int compute_level_populations(const bool use_Ng_acceleration, const long max_niterations) {
+    int compute_level_populations(const bool use_Ng_acceleration, const long max_niterations) { return level_population_loop(use_Ng_acceleration, max_niterations, false); }
+    // ---- Model::compute_level_populations_sparse (model.cpp:756-850): the same loop over the memory-sparse radiation field ----
+    int compute_level_populations_sparse(const bool use_Ng_acceleration, const long max_niterations) { return level_population_loop(use_Ng_acceleration, max_niterations, true); }
+    int level_population_loop(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
         if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
         int iteration = 0, iteration_normal = 0;
         error_mean.clear(); error_max.clear();
@@ -676,10 +744,10 @@ class Model {
                 iteration++;
                 some_not_converged = false;
                 const double t0 = now();
-                compute_radiation_field_feautrier_order_2();
-                compute_Jeff();
+                if (sparse) { compute_radiation_field_feautrier_order_2_sparse(); compute_Jeff_sparse(); }
+                else { compute_radiation_field_feautrier_order_2(); compute_Jeff(); }
                 const double t1 = now();
-                compute_level_populations_from_stateq();
+                if (sparse) compute_level_populations_from_stateq_sparse(); else compute_level_populations_from_stateq();
                 const double t2 = now();
                 seconds_radiation_field += t1 - t0; seconds_statistical_equilibrium += t2 - t1;
                 iteration_normal++;

@@ -12,13 +12,13 @@ import util
 CASES = ["c1_all_constant", "c2_vanzadelhoff", "wind3d_small", "wind3d_spiral_2spec"]
 
 
-def assert_populations_close(got, want, tot, ctx=""):
+def assert_populations_close(got, want, tot, ctx="", abs_tot=1e-15):
     """1e-10 relative (BASELINE.json north_star) plus an absolute term of 1e-15 of the point's total population: the two
     long-double LU factorisations (dense per block here, global SparseLU/COLAMD in the reference) agree to ~1e-17 of the
     total, which for a level holding less than 1e-7 of the molecules is more than 1e-10 of that level -- solver noise
     that the reference's result carries itself (it also ignores levels below 1e-10 of the total when testing convergence)."""
     want = np.asarray(want).reshape(got.shape)
-    bound = 1e-10 * np.abs(want) + 1e-15 * np.asarray(tot)[:, None]
+    bound = 1e-10 * np.abs(want) + abs_tot * np.asarray(tot)[:, None]
     bad = np.abs(got - want) > bound
     assert not bad.any(), f"{ctx}: {bad.sum()} populations differ, worst {np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300))}"
 
