@@ -201,7 +201,7 @@ def run_reference(args):
     ms = 1e3 * float(np.mean(times))
     solves = N * R * nfreqs
     val = solves / (ms * 1e-3)
-    print(json.dumps({"impl": "reference", "metric": "point*ray*freq Feautrier order-2 solves/s", "value": val, "unit": "solves/s",
+    emit(({"impl": "reference", "metric": "point*ray*freq Feautrier order-2 solves/s", "value": val, "unit": "solves/s",
                       "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
                       "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                       "config": cfg, "cpu_baseline": {"value": val, "unit": "solves/s", "cores": cores, "kind": kind,
@@ -422,12 +422,27 @@ def run_b200(args):
         dist.barrier()
         dist.destroy_process_group()
     if out is not None:
-        print(json.dumps(out))
+        emit(out)
+
+
+_STDOUT_FD = None
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _STDOUT_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_STDOUT_FD, line)
 
 
 def main():
-    # rank 0 prints exactly ONE line on stdout: NCCL's own version/debug lines (NCCL_DEBUG=VERSION/INFO on some boxes) go to stderr
-    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    # rank 0 prints exactly ONE line on stdout. Libraries write there too (NCCL prints "NCCL version ..." from C, whatever NCCL_DEBUG_FILE
+    # says): file descriptor 1 is pointed at stderr for the whole run and the JSON line goes to the saved descriptor (emit()).
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     args = parse()
     if args.impl == "reference":
         run_reference(args)

@@ -26,7 +26,7 @@ def main():
         ctx = cabi.Context(local)
         ctx.set_model(flat)
         ctx.run(approx)
-        J1 = ctx.get_J(); L1 = ctx.get_lambda()
+        J1 = ctx.get_J(); L1 = ctx.get_lambda(); JL1 = ctx.get_J_lines()
         uid = [ctx.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(uid, src=0)
         ctx.comm_init(world, rank, uid[0])
@@ -35,8 +35,8 @@ def main():
             ctx.run(approx, rng)
         ctx.allgather()
         N = int(flat["npoints"])
-        Jn = ctx.get_J((0, N)); Ln = ctx.get_lambda((0, N))
-        same = np.array_equal(J1, Jn) and np.array_equal(L1[0], Ln[0]) and np.array_equal(L1[1], Ln[1])
+        Jn = ctx.get_J((0, N)); Ln = ctx.get_lambda((0, N)); JLn = ctx.get_J_lines((0, N))
+        same = np.array_equal(J1, Jn) and np.array_equal(JL1, JLn) and np.array_equal(L1[0], Ln[0]) and np.array_equal(L1[1], Ln[1])
         err = util.relerr(Jn, ref["ref_J"])
         print(f"rank {rank}/{world} {name}: range {rng} gathered==single {same}, max rel err vs reference {err:.2e}", flush=True)
         ok = ok and same and err <= 1e-10
