@@ -176,6 +176,13 @@ typedef struct mgb_image_stats {
 int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
                                 uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
                                 double* ImX, double* ImY, double* I, mgb_image_stats* stats);
+/* Model::compute_image_optical_depth_new(raydir, Nxpix, Nypix) (model.cpp:1102-1127) -> Solver::image_optical_depth_new_imager<approx>
+ * (solver.tpp:688-733) with Solver::image_optical_depth (:2718-2760): same surface, start search and trace as above; the image holds
+ * the optical depth along each pixel's ray per frequency bin (0 for a ray without interior points). Same arguments and errors
+ * (the OneLine text is the reference's "One line approximation is currently not supported for imaging."). */
+int mgb_image_optical_depth(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                                uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
+                                double* ImX, double* ImY, double* tau, mgb_image_stats* stats);
 
 /* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
 /* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */

@@ -18,7 +18,7 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
-    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines",
+    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth",
 ]
 
 
@@ -171,8 +171,10 @@ class Context:
         self._check(self.lib.mgb_set_line_state(self._ctx, pe, po, pw, pt), "mgb_set_line_state")
 
     # ---- run --------------------------------------------------------------------------------
-    def image(self, approx, dimension, ray_dir, nx, ny, nu, pix_range=None):
-        """mgb_image_feautrier_order_2: nu is [nfreqs] (common bins) or [npoints][nfreqs]. -> (ImX, ImY, I[pixels][nfreqs], stats)"""
+    def image(self, approx, dimension, ray_dir, nx, ny, nu, pix_range=None, optical_depth=False):
+        """mgb_image_feautrier_order_2 (or mgb_image_optical_depth): nu is [nfreqs] (common bins) or [npoints][nfreqs].
+        -> (ImX, ImY, I[pixels][nfreqs], stats)"""
+        fn = self.lib.mgb_image_optical_depth if optical_depth else self.lib.mgb_image_feautrier_order_2
         nu, pnu = _p(nu, np.float64)
         per_point = 1 if nu.ndim == 2 else 0
         nfreqs = nu.shape[-1]
@@ -180,7 +182,7 @@ class Context:
         p0, p1 = pix_range or (0, nx * ny)
         X, Y, I = np.empty(nx * ny), np.empty(nx * ny), np.empty((p1 - p0, nfreqs))
         st = ImageStats()
-        self._check(self.lib.mgb_image_feautrier_order_2(self._ctx, C.c_int(approx), C.c_int(dimension), pd, C.c_uint32(nx), C.c_uint32(ny),
+        self._check(fn(self._ctx, C.c_int(approx), C.c_int(dimension), pd, C.c_uint32(nx), C.c_uint32(ny),
                                                          C.c_uint32(nfreqs), pnu, C.c_int(per_point), C.c_uint64(p0), C.c_uint64(p1),
                                                          X.ctypes.data_as(C.c_void_p), Y.ctypes.data_as(C.c_void_p),
                                                          I.ctypes.data_as(C.c_void_p), C.byref(st)), "mgb_image_feautrier_order_2")

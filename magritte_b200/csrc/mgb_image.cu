@@ -231,7 +231,9 @@ __device__ __forceinline__ void image_source_dtau(const DevModel& m, const Entry
     }
 }
 
-template <int APPROX>
+// TAU: Solver::image_optical_depth (solver.tpp:2718-2760) instead -- the same walk, Image.I = sum of the segments' dtau from the far end
+// to the start point (image_optical_depth_new_imager, :688-733; 0 for a ray without interior points).
+template <int APPROX, bool TAU>
 __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, uint32_t nfreqs, uint32_t nchunks_f,
                                                      const double* __restrict__ nu, uint32_t nu_stride,
                                                      const uint32_t* __restrict__ len, const uint32_t* __restrict__ start,
@@ -249,7 +251,26 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
     const double freq  = __ldg(&nu[(size_t)c * nu_stride + f]);
     double out;
     if (L == 0) {
-        out = boundary_intensity(m, c, freq); /* n_tot = 1 (solver.tpp:616-620) */
+        out = TAU ? 0.0 : boundary_intensity(m, c, freq); /* n_tot = 1 (solver.tpp:616-620; :726-730) */
+    } else if (TAU) {
+        const unsigned long long off = ip.poff[pix];
+        Entry cur, nxt;
+        cur.p1 = ip.nr[off + L - 1]; cur.p2 = ip.nri[off + L - 1]; cur.factor = ip.fac[off + L - 1]; cur.shift = ip.sh[off + L - 1];
+        bool compute_curr_opacity = true;
+        double chi_c = 0.0, chi_n = 0.0, term_c = 0.0, term_n = 0.0, dtau_n = 0.0, tau = 0.0;
+        for (uint32_t e = L; e-- > 0;) {
+            if (e > 0) {
+                nxt.p1 = ip.nr[off + e - 1]; nxt.p2 = ip.nri[off + e - 1]; nxt.factor = ip.fac[off + e - 1]; nxt.shift = ip.sh[off + e - 1];
+            } else {
+                nxt.p1 = c; nxt.p2 = 0u; nxt.factor = 0.0; nxt.shift = shift0[pix];
+            }
+            if (e != L - 1) { term_c = term_n; chi_c = chi_n; }
+            image_source_dtau<APPROX>(m, cur, nxt, freq * cur.shift, freq * nxt.shift, ip.dz[off + e], compute_curr_opacity, dtau_n, chi_c, chi_n,
+                                      term_c, term_n);
+            tau += dtau_n;
+            cur = nxt;
+        }
+        out = tau;
     } else {
         const unsigned long long off = ip.poff[pix];
         Entry cur, nxt;
@@ -380,9 +401,9 @@ void projection_surface(const mgb_ctx* ctx, int dimension, ImageGeom& g, uint32_
 
 #define MGB_TRY_(x) do { int rc_ = (x); if (rc_ != MGB_OK) return rc_; } while (0)
 
-extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
-                                           uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
-                                           double* ImX_out, double* ImY_out, double* I_out, mgb_image_stats* stats) {
+static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                      uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end, double* ImX_out,
+                      double* ImY_out, double* I_out, mgb_image_stats* stats) {
     if (!ctx) return MGB_EINVAL;
     if (!(ctx->have_geometry && ctx->have_thermo && ctx->have_lines && ctx->have_state))
         return ctx->fail(MGB_ESTATE, "mgb_image_feautrier_order_2: model incomplete (geometry %d thermo %d lines %d state %d)",
@@ -396,7 +417,9 @@ extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimensi
     const double n2 = ray_dir[0] * ray_dir[0] + ray_dir[1] * ray_dir[1] + ray_dir[2] * ray_dir[2];
     if (n2 == 0.0) return ctx->fail(MGB_EINVAL, "The given ray direction vector does not point in a direction. Please use a non-zero (normed) "
                                                 "direction vector to generate an image.");
-    if (approx == APPROX_ONELINE) return ctx->fail(MGB_EUNSUPPORTED, "One line approximation is not supported for imaging.");
+    if (approx == APPROX_ONELINE)
+        return ctx->fail(MGB_EUNSUPPORTED, optical_depth ? "One line approximation is currently not supported for imaging."
+                                                         : "One line approximation is not supported for imaging.");
     if (approx != APPROX_NONE && approx != APPROX_CLOSELINES) return ctx->fail(MGB_EINVAL, "approx must be 0 (None) or 2 (CloseLines)");
     if (dimension != 1 && dimension != 3) return ctx->fail(MGB_EINVAL, "dimension must be 1 or 3 (Image::set_coordinates_projection_surface)");
     ImageGeom g;
@@ -478,14 +501,13 @@ extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimensi
         const size_t nitems = (size_t)np * nchunks_f;
         const unsigned blocks = (unsigned)((nitems * 32 + 127) / 128);
         const uint32_t stride = nu_per_point ? nfreqs : 0u;
-        if (approx == APPROX_NONE)
-            k_image_solve<APPROX_NONE><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,
-                                                                        ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip,
-                                                                        ctx->im_I.as<double>());
-        else
-            k_image_solve<APPROX_CLOSELINES><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,
-                                                                              ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0,
-                                                                              ip, ctx->im_I.as<double>());
+#define MGB_IMAGE_LAUNCH(A, T)                                                                                                          \
+    k_image_solve<A, T><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,              \
+                                                         ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip,         \
+                                                         ctx->im_I.as<double>())
+        if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
+        else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
+#undef MGB_IMAGE_LAUNCH
         MGB_CUDA(ctx, cudaGetLastError());
         st.n_launches++;
         st.ms_solve += tt.stop();
@@ -497,4 +519,16 @@ extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimensi
     st.n_pixels = npix; st.n_solves = (uint64_t)npix * nfreqs; st.start_bdy = g.start_bdy;
     if (stats) *stats = st;
     return MGB_OK;
+}
+
+extern "C" int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                                           uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
+                                           double* ImX_out, double* ImY_out, double* I_out, mgb_image_stats* stats) {
+    return image_impl(ctx, false, approx, dimension, ray_dir, nx, ny, nfreqs, nu, nu_per_point, pix_begin, pix_end, ImX_out, ImY_out, I_out, stats);
+}
+
+extern "C" int mgb_image_optical_depth(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
+                                       uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
+                                       double* ImX_out, double* ImY_out, double* tau_out, mgb_image_stats* stats) {
+    return image_impl(ctx, true, approx, dimension, ray_dir, nx, ny, nfreqs, nu, nu_per_point, pix_begin, pix_end, ImX_out, ImY_out, tau_out, stats);
 }

@@ -47,6 +47,7 @@ PYBIND11_MODULE(core, m) {
 
     py::class_<Image>(m, "Image")
         .def_readonly("nfreqs", &Image::nfreqs)
+        .def_readonly("optical_depth", &Image::optical_depth)
         .def_property_readonly("ImX", [](const Image& i) { return py::array_t<double>(i.ImX.size(), i.ImX.data()); })
         .def_property_readonly("ImY", [](const Image& i) { return py::array_t<double>(i.ImY.size(), i.ImY.data()); })
         .def_property_readonly("freqs", [](const Image& i) { return py::array_t<double>(i.freqs.size(), i.freqs.data()); })
@@ -109,6 +110,7 @@ PYBIND11_MODULE(core, m) {
         .def("compute_level_populations_from_stateq_sparse", &Model::compute_level_populations_from_stateq_sparse)
         .def("compute_level_populations_sparse", &Model::compute_level_populations_sparse)
         .def("compute_image_new", &Model::compute_image_new)
+        .def("compute_image_optical_depth_new", &Model::compute_image_optical_depth_new)
         // test hook: radiation.J and the diagonal Lambda lists as a radiation-field call leaves them (host-only tests of compute_Jeff / stateq)
         .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt) {
             s.J = vec(J);

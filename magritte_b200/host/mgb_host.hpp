@@ -418,6 +418,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
 
 struct Image { // reference src/model/image/image.hpp (the fields the new imager fills)
     Size nx = 0, ny = 0, nfreqs = 0;
+    bool optical_depth = false; // ImageType::OpticalDepth (image.hpp) instead of Intensity
     double ray_direction[3] = {0, 0, 0};
     std::vector<double> ImX, ImY, I, freqs; // I [nx*ny][nfreqs]
 };
@@ -761,12 +762,17 @@ class Model {
         return iteration;
     }
     // ---- Model::compute_image_new(rx, ry, rz, Nxpix, Nypix) (model.cpp:999-1035) ----
-    int compute_image_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) {
+    int compute_image_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) { return image_new(false, rx, ry, rz, Nxpix, Nypix); }
+    // ---- Model::compute_image_optical_depth_new(raydir, Nxpix, Nypix) (model.cpp:1102-1127): Image.I holds optical depths ----
+    int compute_image_optical_depth_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) { return image_new(true, rx, ry, rz, Nxpix, Nypix); }
+    int image_new(const bool optical_depth, const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) {
         if (rx * rx + ry * ry + rz * rz == 0.0)
             throw std::runtime_error("The given ray direction vector does not point in a direction. Please use a non-zero (normed) direction vector to generate an image.");
-        if (parameters.one_line_approximation) throw std::runtime_error("One line approximation is not supported for imaging.");
+        if (parameters.one_line_approximation)
+            throw std::runtime_error(optical_depth ? "One line approximation is currently not supported for imaging." : "One line approximation is not supported for imaging.");
         sync_static(false);
         Image im;
+        im.optical_depth = optical_depth;
         im.nx = Nxpix; im.ny = Nypix; im.nfreqs = nfreqs;
         const double n = 1 / std::sqrt(rx * rx + ry * ry + rz * rz);
         im.ray_direction[0] = rx * n; im.ray_direction[1] = ry * n; im.ray_direction[2] = rz * n;
@@ -778,8 +784,10 @@ class Model {
         std::vector<double> ptot((size_t)nlspecs() * npoints);
         for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
         check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
-        check(mgb_image_feautrier_order_2(ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(),
-                                          per_point ? 1 : 0, 0, npix, im.ImX.data(), im.ImY.data(), im.I.data(), nullptr), "mgb_image_feautrier_order_2");
+        check((optical_depth ? mgb_image_optical_depth : mgb_image_feautrier_order_2)(
+                  ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(), per_point ? 1 : 0, 0,
+                  npix, im.ImX.data(), im.ImY.data(), im.I.data(), nullptr),
+              optical_depth ? "mgb_image_optical_depth" : "mgb_image_feautrier_order_2");
         images.push_back(std::move(im));
         return 0;
     }

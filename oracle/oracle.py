@@ -126,7 +126,7 @@ class Oracle:
         assert rc == 0
         return self.J
 
-    def image(self, ray_dir, nx, ny, dimension):
+    def image(self, ray_dir, nx, ny, dimension, optical_depth=False):
         """The new imager (Solver::image_feautrier_order_2_new_imager) on the model's current frequency discretisation.
         ray_dir is normed here like Model::compute_image_new does (model.cpp:1014). -> dict(ImX, ImY, I, start_pt, n_tot)."""
         m = self.m
@@ -137,7 +137,8 @@ class Oracle:
         sp, nt = np.zeros(npix, np.uint32), np.zeros(npix, np.uint32)
         if self.threads:
             os.environ["OMP_NUM_THREADS"] = str(self.threads)
-        rc = self.lib.orc_image(C.byref(m), C.c_int(dimension), _ptr(r, _f64p), C.c_uint32(nx), C.c_uint32(ny), _ptr(ImX, _f64p),
+        fn = self.lib.orc_image_optical_depth if optical_depth else self.lib.orc_image
+        rc = fn(C.byref(m), C.c_int(dimension), _ptr(r, _f64p), C.c_uint32(nx), C.c_uint32(ny), _ptr(ImX, _f64p),
                                 _ptr(ImY, _f64p), _ptr(I, _f64p), _ptr(sp, _u32p), _ptr(nt, _u32p))
         assert rc == 0
         return dict(ImX=ImX, ImY=ImY, I=I, start_pt=sp, n_tot=nt)

@@ -31,6 +31,20 @@ def test_image_against_reference(ctx, name):
         assert st.n_solves == I.size
 
 
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_optical_depth_image_against_reference(ctx, name):
+    """mgb_image_optical_depth against Model::compute_image_optical_depth_new of the compiled reference (same summation order)."""
+    from magritte_b200.flatten import approx_of
+    flat, img = util.load_golden_image(name)
+    ctx.set_model(flat, frequencies=False)
+    approx = approx_of(flat["params"])
+    for d, (X, Y, T) in zip(img["directions"], util.load_golden_image_tau(name)):
+        gX, gY, gT, st = ctx.image(approx, img["dimension"], d, img["nx"], img["ny"], flat["nu_image"], optical_depth=True)
+        assert np.array_equal(gX, X) and np.array_equal(gY, Y)
+        assert util.relerr(gT, T) <= 1e-10, f"{name} {d}"
+        assert np.array_equal(gT, T), f"{name} {d}: not bit-identical, max rel err {util.relerr(gT, T)}"
+
+
 def test_image_options_and_errors(ctx):
     """Per-point frequency rows, pixel sub-ranges, small chunks (bounded storage) and ApproximationType None give the same
     image; the reference's exceptions map to error codes."""

@@ -55,3 +55,7 @@ def test_image_through_host_model():
     im = m.images[-1]
     assert np.array_equal(im.ImX, X) and np.array_equal(im.ImY, Y)
     assert util.relerr(im.I, I) <= 1e-10
+    # the optical-depth image of the same pixels through the same host method family (Model::compute_image_optical_depth_new)
+    m.compute_image_optical_depth_new(float(d[0]), float(d[1]), float(d[2]), img["nx"], img["ny"])
+    tau = m.images[-1]
+    assert tau.optical_depth and np.array_equal(np.asarray(tau.I).reshape(-1), util.load_golden_image_tau("wind3d_small")[1][2].reshape(-1))

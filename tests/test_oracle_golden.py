@@ -48,6 +48,17 @@ def test_oracle_image_bit_exact(name):
 
 
 @pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_oracle_optical_depth_image_bit_exact(name):
+    """Solver::image_optical_depth_new_imager restated: Image.I (optical depth) of the compiled reference, bit for bit."""
+    flat, img = util.load_golden_image(name)
+    o = orc.Oracle(flat, store_u=False)
+    for d, (X, Y, T) in zip(img["directions"], util.load_golden_image_tau(name)):
+        r = o.image(d, img["nx"], img["ny"], img["dimension"], optical_depth=True)
+        assert np.array_equal(r["ImX"], X) and np.array_equal(r["ImY"], Y)
+        assert np.array_equal(r["I"], T), f"{name} {d}: max rel err {util.relerr(r['I'], T)}"
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
 def test_oracle_banded_lambda_bit_exact(name):
     """n_off_diag > 0: the oracle's Lambda lists equal the compiled reference's, element for element in insertion order."""
     flat, ref = util.load_golden_offdiag(name)

@@ -119,6 +119,14 @@ def load_golden_image(name):
     return flat, img
 
 
+def load_golden_image_tau(name):
+    """Optical-depth images of the same model, bins, directions and pixels as load_golden_image (tests/golden/make_golden_image_tau.py):
+    -> [(ImX, ImY, tau)] per direction."""
+    z = np.load(os.path.join(GOLDEN, f"imagetau_{name}.npz"))
+    n = len([k for k in z.files if k.startswith("tau_")])
+    return [(z[f"ImX_{i}"], z[f"ImY_{i}"], z[f"tau_{i}"]) for i in range(n)]
+
+
 def load_golden_offdiag(name):
     """-> (flat inputs with params.n_off_diag = K, dict(J, lambda_val/nr/cnt [N][L][cap] in the reference's insertion order))."""
     flat, _ = load_golden(name)
