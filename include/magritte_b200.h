@@ -184,6 +184,14 @@ int mgb_image_optical_depth(mgb_ctx* ctx, int approx, int dimension, const doubl
                                 uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
                                 double* ImX, double* ImY, double* tau, mgb_image_stats* stats);
 
+/* ---- column densities ---------------------------------------------------- */
+/* Model::set_column (model.cpp:1143-1154) -> Solver::set_column / get_column (solver.tpp:2953-2991): for origins o in
+ * [o_begin, o_end) and every ray r, the trapezoid sum of 0.5 * (density[crt] + density[nxt]) * dZ over the geometric steps of
+ * the half-ray, outward from the origin (0 for a ray that leaves the model at once). density [npoints] (Model::density, host);
+ * column [nrays][o_end-o_begin] (rows of Model::column, host). Needs the geometry only. ms_kernel (may be NULL): device time
+ * of the kernel. A ray that dead-ends inside the model stops there (the reference would index density[npoints]). */
+int mgb_set_column(mgb_ctx* ctx, const double* density, uint32_t o_begin, uint32_t o_end, double* column, float* ms_kernel);
+
 /* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
 /* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */
 int mgb_nccl_unique_id(void* id128);

@@ -18,7 +18,7 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
-    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth",
+    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
 ]
 
 
@@ -171,6 +171,16 @@ class Context:
         self._check(self.lib.mgb_set_line_state(self._ctx, pe, po, pw, pt), "mgb_set_line_state")
 
     # ---- run --------------------------------------------------------------------------------
+    def set_column(self, density, o_range=None, with_time=False):
+        """mgb_set_column: Model::set_column for origins o_range -> column [nrays][o1-o0] (and the kernel's device ms)."""
+        rho, prho = _p(density, np.float64)
+        o0, o1 = o_range or (0, self.npoints)
+        col = np.empty((self.nrays, max(o1 - o0, 0)))
+        ms = C.c_float(0)
+        self._check(self.lib.mgb_set_column(self._ctx, prho, C.c_uint32(o0), C.c_uint32(o1), col.ctypes.data_as(C.c_void_p),
+                                            C.byref(ms)), "mgb_set_column")
+        return (col, ms.value) if with_time else col
+
     def image(self, approx, dimension, ray_dir, nx, ny, nu, pix_range=None, optical_depth=False):
         """mgb_image_feautrier_order_2 (or mgb_image_optical_depth): nu is [nfreqs] (common bins) or [npoints][nfreqs].
         -> (ImX, ImY, I[pixels][nfreqs], stats)"""

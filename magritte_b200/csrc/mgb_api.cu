@@ -669,6 +669,30 @@ extern "C" int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const doubl
     return MGB_OK;
 }
 
+// Model::set_column (model.cpp:1143-1154) -> Solver::set_column / get_column (solver.tpp:2953-2991).
+extern "C" int mgb_set_column(mgb_ctx* ctx, const double* density, uint32_t o_begin, uint32_t o_end, double* column, float* ms_kernel) {
+    if (!ctx || !density || !column) return MGB_EINVAL;
+    if (!ctx->have_geometry) return ctx->fail(MGB_ESTATE, "mgb_set_column before mgb_set_geometry");
+    const DevModel& m = ctx->m;
+    if (o_begin >= o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "mgb_set_column: bad origin range [%u,%u)", o_begin, o_end);
+    cudaSetDevice(ctx->device);
+    const uint32_t no = o_end - o_begin;
+    const size_t nw   = (size_t)no * m.nrays;
+    DevBuf rho, col;
+    MGB_CUDA(ctx, rho.ensure(8 * (size_t)m.npoints));
+    MGB_CUDA(ctx, col.ensure(8 * nw));
+    MGB_CUDA(ctx, cudaMemcpyAsync(rho.p, density, 8 * (size_t)m.npoints, cudaMemcpyHostToDevice, ctx->stream));
+    EventTimer t(ctx->stream);
+    t.start();
+    k_column<<<(unsigned)((nw * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, o_begin, no, rho.as<double>(), col.as<double>());
+    MGB_CUDA(ctx, cudaGetLastError());
+    const float ms = t.stop();
+    if (ms_kernel) *ms_kernel = ms;
+    MGB_CUDA(ctx, cudaMemcpyAsync(column, col.p, 8 * nw, cudaMemcpyDeviceToHost, ctx->stream));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return MGB_OK;
+}
+
 extern "C" int mgb_result_ptrs_dev(mgb_ctx* ctx, void** J_dev, void** lambda_val_dev, void** lambda_cnt_dev) {
     if (!ctx) return MGB_EINVAL;
     if (!ctx->J.p) return ctx->fail(MGB_ESTATE, "mgb_result_ptrs_dev: no results yet");

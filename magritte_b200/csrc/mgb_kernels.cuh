@@ -4,6 +4,7 @@
 //   k_trace<FILL>    one warp per half-ray (o, r): count pass / fill pass of the geometric path
 //   k_solve<APPROX>  one warp per (o, rr, 32 frequencies): lanes = frequency bins; eta/chi assembly and
 //                    the two-sided Thomas sweep entirely in registers
+//   k_column         one warp per half-ray: column density of Model::density (Solver::get_column)
 //   k_reduce_J / k_reduce_lambda   J(o,f) and Lambda(o,k) accumulated in the reference's summation order
 #pragma once
 #include "mgb_device.cuh"
@@ -109,6 +110,34 @@ __global__ void __launch_bounds__(128) k_trace(DevModel m, uint32_t o0, uint32_t
         atomicAdd(&counters[1], (unsigned long long)scanned);
         atomicMax((unsigned int*)&counters[2], len);
     }
+}
+
+// Column density. reference: Solver::get_column (solver.tpp:2968-2991), driven by Solver::set_column (:2953-2966).
+// One warp per half-ray (o, r) on the same walker as k_trace; lane 0 keeps the running trapezoid sum in the reference's
+// order (outward from the origin). column is [nrays][no] (Model::column rows of this origin range).
+__global__ void __launch_bounds__(128) k_column(DevModel m, uint32_t o0, uint32_t no, const double* __restrict__ density,
+                                                double* __restrict__ column) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t w      = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (w >= (size_t)no * m.nrays) return;
+    const uint32_t ol = (uint32_t)(w / m.nrays), r = (uint32_t)(w % m.nrays);
+    const uint32_t o  = o0 + ol;
+    const RayFrame fr = make_frame(m, o, r);
+    double Z = 0.0, dZ = 0.0, col = 0.0;
+    uint32_t ns;
+    uint32_t nxt = warp_get_next(m, fr, o, Z, dZ, ns, lane);
+    if (nxt < m.npoints) {
+        double rho_crt = __ldg(&density[o]);
+        for (;;) {
+            const double rho_nxt = __ldg(&density[nxt]);
+            col = __dadd_rn(col, __dmul_rn(__dmul_rn(0.5, __dadd_rn(rho_crt, rho_nxt)), dZ));
+            if (__ldg(&m.p2b[nxt]) != m.npoints) break; /* reached the boundary */
+            rho_crt = rho_nxt;
+            nxt     = warp_get_next(m, fr, nxt, Z, dZ, ns, lane);
+            if (!(nxt < m.npoints)) break; /* dead end (the reference would index density[npoints]) */
+        }
+    }
+    if (lane == 0) column[(size_t)r * no + ol] = col;
 }
 
 // per-origin total of lens over all rays (chunk planning)

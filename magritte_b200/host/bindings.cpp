@@ -111,6 +111,10 @@ PYBIND11_MODULE(core, m) {
         .def("compute_level_populations_sparse", &Model::compute_level_populations_sparse)
         .def("compute_image_new", &Model::compute_image_new)
         .def("compute_image_optical_depth_new", &Model::compute_image_optical_depth_new)
+        .def("set_column", &Model::set_column)
+        .def_property("density", [](const Model& s) { return py::array_t<double>(s.density.size(), s.density.data()); },
+                      [](Model& s, arr<double> d) { s.density = vec(d); })
+        .def_property_readonly("column", [](const Model& s) { return s.column.empty() ? out2(s.column, 0, s.npoints) : out2(s.column, s.nrays, s.npoints); })
         // test hook: radiation.J and the diagonal Lambda lists as a radiation-field call leaves them (host-only tests of compute_Jeff / stateq)
         .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt) {
             s.J = vec(J);

@@ -765,6 +765,24 @@ class Model {
     int compute_image_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) { return image_new(false, rx, ry, rz, Nxpix, Nypix); }
     // ---- Model::compute_image_optical_depth_new(raydir, Nxpix, Nypix) (model.cpp:1102-1127): Image.I holds optical depths ----
     int compute_image_optical_depth_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) { return image_new(true, rx, ry, rz, Nxpix, Nypix); }
+    // ---- Model::set_column (model.cpp:1143-1154; Solver::set_column / get_column, solver.tpp:2953-2991): column [nrays][npoints] ----
+    std::vector<double> density, column; // Model::density [npoints], Model::column [nrays][npoints] (model.hpp:118-119)
+    int set_column() {
+        if (density.size() != npoints) throw std::runtime_error("Model::density must hold one value per point.");
+        if (!ctx) {
+            const int rc = mgb_create(device, &ctx);
+            if (rc != MGB_OK) { ctx = nullptr; throw std::runtime_error(std::string("mgb_create failed: ") + mgb_last_error(nullptr)); }
+        }
+        if (dirty_geometry) {
+            check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
+                                   direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
+                                   boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
+            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true;
+        }
+        column.resize((size_t)nrays * npoints);
+        check(mgb_set_column(ctx, density.data(), 0, npoints, column.data(), nullptr), "mgb_set_column");
+        return 0;
+    }
     int image_new(const bool optical_depth, const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) {
         if (rx * rx + ry * ry + rz * rz == 0.0)
             throw std::runtime_error("The given ray direction vector does not point in a direction. Please use a non-zero (normed) direction vector to generate an image.");

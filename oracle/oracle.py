@@ -142,3 +142,16 @@ class Oracle:
                                 _ptr(ImY, _f64p), _ptr(I, _f64p), _ptr(sp, _u32p), _ptr(nt, _u32p))
         assert rc == 0
         return dict(ImX=ImX, ImY=ImY, I=I, start_pt=sp, n_tot=nt)
+
+    def set_column(self, density, o_range=None):
+        """Model::set_column (model.cpp:1143-1154, Solver::get_column solver.tpp:2968-2991) -> column [nrays][o1-o0]."""
+        m = self.m
+        o0, o1 = o_range or (0, m.npoints)
+        rho = np.ascontiguousarray(density, dtype=np.float64)
+        assert rho.shape == (m.npoints,)
+        col = np.zeros((m.nrays, o1 - o0))
+        if self.threads:
+            os.environ["OMP_NUM_THREADS"] = str(self.threads)
+        rc = self.lib.orc_set_column(C.byref(m), _ptr(rho, _f64p), C.c_uint32(o0), C.c_uint32(o1), _ptr(col, _f64p))
+        assert rc == 0
+        return col

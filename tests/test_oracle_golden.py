@@ -67,3 +67,14 @@ def test_oracle_banded_lambda_bit_exact(name):
     assert np.array_equal(J, ref["J"])
     cap = ref["lambda_nr"].shape[2]
     util.lambda_lists_close(o.L_val[:, :, :cap], o.L_nr[:, :, :cap], o.L_cnt, ref, 0)
+
+
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_oracle_column_bit_exact(name):
+    """orc_set_column against Model::column of the compiled reference (tests/golden/make_golden_column.py): bit for bit."""
+    flat, _ = util.load_golden(name)
+    density, column = util.load_golden_column(name)
+    o = orc.Oracle(flat, store_u=False)
+    assert np.array_equal(o.set_column(density), column)
+    sub = o.set_column(density, o_range=(3, 17))
+    assert np.array_equal(sub, column[:, 3:17])

@@ -127,6 +127,13 @@ def load_golden_image_tau(name):
     return [(z[f"ImX_{i}"], z[f"ImY_{i}"], z[f"tau_{i}"]) for i in range(n)]
 
 
+def load_golden_column(name):
+    """-> (density [npoints], column [nrays][npoints]) of Model::set_column on the model of case_<name>.npz
+    (tests/golden/make_golden_column.py)."""
+    z = np.load(os.path.join(GOLDEN, f"column_{name}.npz"))
+    return np.ascontiguousarray(z["density"]), np.ascontiguousarray(z["column"])
+
+
 def load_golden_offdiag(name):
     """-> (flat inputs with params.n_off_diag = K, dict(J, lambda_val/nr/cnt [N][L][cap] in the reference's insertion order))."""
     flat, _ = load_golden(name)
