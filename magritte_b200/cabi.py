@@ -18,7 +18,7 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
-    "mgb_allgather_results", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
+    "mgb_allgather_results", "mgb_comm_destroy", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
 ]
 
 

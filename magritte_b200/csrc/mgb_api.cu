@@ -76,6 +76,7 @@ extern "C" void mgb_destroy(mgb_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
+    mgb_comm_destroy(ctx);
     delete ctx;
 }
 
@@ -162,6 +163,7 @@ extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* po
     ctx->lens_o0 = ctx->lens_o1 = 0;
     ctx->drop_chunks();
     ctx->points_dirty = true;
+    ctx->res_valid = false;
     return MGB_OK;
 }
 
@@ -362,7 +364,9 @@ int ensure_lens(mgb_ctx* ctx, uint32_t o0, uint32_t o1, mgb_stats* st, uint32_t&
     MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 24, cudaMemcpyDeviceToHost));
     ctx->tot_steps = c[0]; ctx->tot_scanned = c[1]; ctx->max_len = (uint32_t)c[2];
     ctx->lens_o0 = o0; ctx->lens_o1 = o1;
-    ctx->drop_chunks();
+    for (auto* c : ctx->chunks) c->filled = false; /* buffers stay: cudaFree/cudaMalloc of GB-sized buffers costs ~0.3 s once NCCL has
+                                                      peer mappings live (profiles/comm_diag_r2.log) */
+    ctx->plan_cached = false;
     return MGB_OK;
 }
 
@@ -416,6 +420,17 @@ cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc
 // shared with mgb_image.cu: per-point derived tables (sqrtw_max, Model::set_dshift_max) up to date
 int mgb_internal_refresh_points(mgb_ctx* ctx) { return refresh_points(ctx); }
 
+// Result arrays [npoints][...] of the Feautrier run (J, J per line, diagonal Lambda element and list length).
+int mgb_internal_alloc_results(mgb_ctx* ctx) {
+    const DevModel& m = ctx->m;
+    const size_t prow = m.npoints;
+    MGB_CUDA(ctx, ctx->J.ensure(8 * prow * m.nfreqs));
+    MGB_CUDA(ctx, ctx->lam_val.ensure(8 * prow * m.nlines));
+    MGB_CUDA(ctx, ctx->J_lines.ensure(8 * prow * m.nlines));
+    MGB_CUDA(ctx, ctx->lam_cnt.ensure(4 * prow * m.nlines));
+    return MGB_OK;
+}
+
 // Contiguous origin ranges of equal predicted cost: cost(o) = sum over rays of the geometric ray length (the count pass), plus one
 // entry per ray for the origin itself. Every rank computes the same bounds from the same replicated geometry.
 extern "C" int mgb_partition_balanced(mgb_ctx* ctx, int nranks, int rank, uint32_t* o_begin, uint32_t* o_end) {
@@ -446,7 +461,7 @@ extern "C" int mgb_invalidate_paths(mgb_ctx* ctx) {
     for (auto* c : ctx->chunks) c->filled = false;
     ctx->work.filled = false;
     ctx->lens_o0 = ctx->lens_o1 = 0;
-    ctx->drop_chunks();
+    ctx->plan_cached = false; /* the chunk objects keep their device buffers for the next plan */
     return MGB_OK;
 }
 
@@ -475,10 +490,17 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
                          ctx->have_geometry, ctx->have_thermo, ctx->have_lines, ctx->have_freqs, ctx->have_state);
     if (approx < 0 || approx > 2) return ctx->fail(MGB_EINVAL, "approx must be 0 (None), 1 (OneLine) or 2 (CloseLines)");
     DevModel& m = ctx->m;
-    if (o_begin >= o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "origin range [%u,%u) invalid for npoints = %u", o_begin, o_end, m.npoints);
+    if (o_begin > o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "origin range [%u,%u) invalid for npoints = %u", o_begin, o_end, m.npoints);
     cudaSetDevice(ctx->device);
     mgb_stats st;
     memset(&st, 0, sizeof st);
+    if (o_begin == o_end) { /* a rank that owns no origin (nranks > npoints, or a very skewed cost partition): a successful no-op that still
+                               owns result buffers, so that the peers' collective in mgb_allgather_results does not hang on it */
+        MGB_TRY(mgb_internal_alloc_results(ctx));
+        ctx->res_o0 = ctx->res_o1 = o_begin; ctx->res_K = ctx->params.n_off_diag; ctx->res_valid = true;
+        if (stats) *stats = st;
+        return MGB_OK;
+    }
     uint32_t launches = 0;
     EventTimer total(ctx->stream);
     total.start();
@@ -495,29 +517,35 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     const bool cacheable = ctx->params.cache_paths && range_steps * 20ull + (size_t)(o_end - o_begin) * m.nrays * 16ull <= ctx->params.path_cache_bytes;
     const unsigned long long chunk_step_budget = cacheable ? ~0ull : std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / 20ull);
     if (!(ctx->plan_cached && ctx->plan_o0 == o_begin && ctx->plan_o1 == o_end && cacheable)) {
-        ctx->drop_chunks();
+        struct Plan { uint32_t o0, o1; unsigned long long steps; };
+        std::vector<Plan> plan;
         uint32_t o = o_begin;
         while (o < o_end) {
-            PathChunk* ch = new PathChunk();
-            ch->o0 = o;
-            unsigned long long s = 0;
-            while (o < o_end && (o - ch->o0) < max_o_scratch) {
+            Plan pl{o, o, 0};
+            while (o < o_end && (o - pl.o0) < max_o_scratch) {
                 const unsigned long long so = ctx->origin_steps[o - ctx->lens_o0];
-                if (o > ch->o0 && s + so > chunk_step_budget) break;
-                s += so; o++;
+                if (o > pl.o0 && pl.steps + so > chunk_step_budget) break;
+                pl.steps += so; o++;
             }
-            ch->o1 = o; ch->steps = s;
-            ctx->chunks.push_back(ch);
+            pl.o1 = o;
+            plan.push_back(pl);
+        }
+        bool same = plan.size() == ctx->chunks.size();
+        for (size_t i = 0; same && i < plan.size(); i++)
+            same = ctx->chunks[i]->o0 == plan[i].o0 && ctx->chunks[i]->o1 == plan[i].o1 && ctx->chunks[i]->steps == plan[i].steps;
+        if (!same) { /* a different decomposition: new chunk objects (an unchanged one keeps its device buffers and its paths) */
+            ctx->drop_chunks();
+            for (const Plan& pl : plan) {
+                PathChunk* ch = new PathChunk();
+                ch->o0 = pl.o0; ch->o1 = pl.o1; ch->steps = pl.steps;
+                ctx->chunks.push_back(ch);
+            }
         }
         ctx->plan_o0 = o_begin; ctx->plan_o1 = o_end; ctx->plan_cached = cacheable;
     }
-    // ---- outputs ----
-    // rows padded so that an in-place all-gather over nranks equal slices fits (mgb_allgather_results)
-    const size_t prow = (size_t)((m.npoints + ctx->nranks - 1) / ctx->nranks) * ctx->nranks;
-    MGB_CUDA(ctx, ctx->J.ensure(8 * prow * m.nfreqs));
-    MGB_CUDA(ctx, ctx->lam_val.ensure(8 * prow * m.nlines));
-    MGB_CUDA(ctx, ctx->J_lines.ensure(8 * prow * m.nlines));
-    MGB_CUDA(ctx, ctx->lam_cnt.ensure(4 * prow * m.nlines));
+    // ---- outputs: full-size arrays on every rank, each rank fills the rows of its origins (mgb_allgather_results completes them) ----
+    const size_t prow = m.npoints;
+    MGB_TRY(mgb_internal_alloc_results(ctx));
     double* u_full = nullptr;
     if (ctx->params.store_intensities) {
         MGB_CUDA(ctx, ctx->u_full.ensure(8 * (size_t)m.hnrays * (o_end - o_begin) * m.nfreqs));
@@ -588,16 +616,15 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     st.n_chunks = (uint32_t)ctx->chunks.size();
     st.n_launches = launches;
     st.paths_cached = all_cached ? 1 : 0;
-    ctx->res_o0 = o_begin; ctx->res_o1 = o_end;
+    ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true;
     if (stats) *stats = st;
     return MGB_OK;
 }
 
 static int check_range(mgb_ctx* ctx, uint32_t o0, uint32_t o1, const char* who) {
-    if (ctx->res_o1 <= ctx->res_o0) return ctx->fail(MGB_ESTATE, "%s: no results (run first)", who);
-    if (o0 >= o1 || o0 < ctx->res_o0 || o1 > ctx->res_o1)
-        if (!(ctx->nranks > 1 && o1 <= ctx->m.npoints && o0 < o1)) /* after an all-gather every row is valid */
-            return ctx->fail(MGB_EINVAL, "%s: range [%u,%u) outside the computed range [%u,%u)", who, o0, o1, ctx->res_o0, ctx->res_o1);
+    if (!ctx->res_valid) return ctx->fail(MGB_ESTATE, "%s: no results (run first)", who);
+    if (o0 >= o1 || o0 < ctx->res_o0 || o1 > ctx->res_o1) /* mgb_allgather_results widens the valid range to [0, npoints) */
+        return ctx->fail(MGB_EINVAL, "%s: range [%u,%u) outside the computed range [%u,%u)", who, o0, o1, ctx->res_o0, ctx->res_o1);
     return MGB_OK;
 }
 
@@ -631,14 +658,15 @@ extern "C" int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, do
 
 extern "C" int mgb_lambda_capacity(mgb_ctx* ctx, uint32_t* cap) {
     if (!ctx || !cap) return MGB_EINVAL;
-    *cap = ctx->params.n_off_diag ? 1 + 2 * ctx->params.n_off_diag * ctx->m.hnrays : 1;
+    /* the capacity of the lists the LAST RUN produced (what mgb_get_lambda_lists copies), not of the current parameters */
+    *cap = ctx->res_valid ? ctx->lam_cap : (ctx->params.n_off_diag ? 1 + 2 * ctx->params.n_off_diag * ctx->m.hnrays : 1);
     return MGB_OK;
 }
 
 extern "C" int mgb_get_lambda_lists(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* list_val, uint32_t* list_nr, uint32_t* list_cnt) {
     if (!ctx || !list_val || !list_nr || !list_cnt) return MGB_EINVAL;
     MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_lambda_lists"));
-    if (!ctx->params.n_off_diag || !ctx->lam_list_val.p) return ctx->fail(MGB_ESTATE, "mgb_get_lambda_lists: the last run had n_off_diag = 0 (use mgb_get_lambda)");
+    if (!ctx->res_K || !ctx->lam_list_val.p) return ctx->fail(MGB_ESTATE, "mgb_get_lambda_lists: the last run had n_off_diag = 0 (use mgb_get_lambda)");
     cudaSetDevice(ctx->device);
     const size_t L = ctx->m.nlines, n = (size_t)(o_end - o_begin) * L, cap = ctx->lam_cap;
     MGB_CUDA(ctx, cudaMemcpy(list_val, ctx->lam_list_val.as<double>() + (size_t)o_begin * L * cap, 8 * n * cap, cudaMemcpyDeviceToHost));

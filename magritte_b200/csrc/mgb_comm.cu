@@ -59,7 +59,20 @@ extern "C" int mgb_comm_init(mgb_ctx* ctx, int nranks, int rank, const void* id1
     ncclComm_t comm = nullptr;
     const ncclResult_t r = g_nccl.CommInitRank(&comm, nranks, id, rank);
     if (r != 0) return ctx->fail(MGB_ENCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(r));
+    if (ctx->comm) g_nccl.CommDestroy((ncclComm_t)ctx->comm);
     ctx->comm = comm; ctx->nranks = nranks; ctx->rank = rank;
+    return MGB_OK;
+}
+
+// mgb_destroy calls this; also exported so that a host can drop the communicator and keep the context.
+extern "C" int mgb_comm_destroy(mgb_ctx* ctx) {
+    if (!ctx) return MGB_EINVAL;
+    if (ctx->comm && g_nccl.h) {
+        cudaSetDevice(ctx->device);
+        g_nccl.CommDestroy((ncclComm_t)ctx->comm);
+    }
+    ctx->comm = nullptr; ctx->nranks = 1; ctx->rank = 0;
+    ctx->part_bounds.clear();
     return MGB_OK;
 }
 
@@ -91,8 +104,10 @@ extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
     if (!ctx) return MGB_EINVAL;
     if (ctx->nranks == 1) return MGB_OK;
     if (!ctx->comm) return ctx->fail(MGB_ESTATE, "mgb_allgather_results: mgb_comm_init was not called");
-    if (!ctx->J.p) return ctx->fail(MGB_ESTATE, "mgb_allgather_results: no results");
     cudaSetDevice(ctx->device);
+    /* Every rank must enter the collective: a rank without results of its own (empty origin range) still owns the buffers. A rank whose
+       run FAILED must not come here alone -- callers agree on the error first (the host Model reduces the status over the ranks). */
+    if (!ctx->J.p) { const int rc = mgb_internal_alloc_results(ctx); if (rc != MGB_OK) return rc; }
     const mgb::DevModel& m = ctx->m;
     if ((int)ctx->part_bounds.size() != ctx->nranks + 1)
         return ctx->fail(MGB_ESTATE, "mgb_allgather_results: call mgb_partition or mgb_partition_balanced with nranks = %d first", ctx->nranks);
@@ -112,6 +127,6 @@ extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
     const ncclResult_t r2 = g_nccl.GroupEnd();
     if (r || r2) return ctx->fail(MGB_ENCCL, "ncclBroadcast (all-gather of origin slices): %s", g_nccl.GetErrorString(r ? r : r2));
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->res_o0 = 0; ctx->res_o1 = m.npoints;
+    ctx->res_o0 = 0; ctx->res_o1 = m.npoints; ctx->res_valid = true;
     return MGB_OK;
 }

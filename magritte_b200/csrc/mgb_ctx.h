@@ -71,6 +71,8 @@ struct mgb_ctx {
     uint32_t lam_cap = 1;
     uint32_t u_o0 = 0, u_no = 0;
     uint32_t res_o0 = 0, res_o1 = 0; // origin range of the last run
+    uint32_t res_K = 0;              // n_off_diag of the last run (lam_cap is that run's list capacity)
+    bool res_valid = false;
     // tracing state
     mgb::DevBuf lens;       // [npoints][nrays]
     uint32_t lens_o0 = 0, lens_o1 = 0;
@@ -114,6 +116,7 @@ struct mgb_ctx {
 };
 
 int mgb_internal_refresh_points(mgb_ctx* ctx); // mgb_api.cu
+int mgb_internal_alloc_results(mgb_ctx* ctx);  // mgb_api.cu
 
 #define MGB_CUDA(ctx, call)                                                                                         \
     do {                                                                                                            \
