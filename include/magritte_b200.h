@@ -25,7 +25,7 @@
 extern "C" {
 #endif
 
-#define MGB_ABI_VERSION 1
+#define MGB_ABI_VERSION 2
 
 enum { MGB_OK = 0, MGB_EINVAL = -1, MGB_ECUDA = -2, MGB_ESTATE = -3, MGB_ENOMEM = -4, MGB_EUNSUPPORTED = -5, MGB_ENCCL = -6 };
 
@@ -140,6 +140,9 @@ int mgb_solve_feautrier_order_2(mgb_ctx* ctx, int approx, const double* emissivi
                                 const double* inverse_width, const double* population_tot, uint32_t o_begin,
                                 uint32_t o_end, double* J, double* lambda_val, uint32_t* lambda_cnt, double* u,
                                 mgb_stats* stats);
+/* Install a radiation field computed elsewhere (a checkpoint, another run) as the result of the last run: radiation.J [npoints][nfreqs],
+ * J per line [npoints][nlines] (either may be NULL: left as it is), the diagonal Lambda element and list length [npoints][nlines]. */
+int mgb_set_radiation_field(mgb_ctx* ctx, const double* J, const double* J_lines, const double* lambda_val, const uint32_t* lambda_cnt);
 /* Device addresses of the result buffers (full-size [npoints][nfreqs] / [npoints][nlines]) for in-place
  * collectives: replaces Radiation::MPI_reduce_J / Lambda::MPI_gather (radiation.cpp:76-91, lambda.tpp:121-206). */
 int mgb_result_ptrs_dev(mgb_ctx* ctx, void** J_dev, void** lambda_val_dev, void** lambda_cnt_dev);
@@ -210,6 +213,61 @@ int mgb_partition_rows(uint32_t npoints, int nranks, int rank, uint32_t* o_begin
  * alone -- the callers agree on the error first (the host Model all-reduces the status). Measured 0.5 ms for 485 MB on 2 B200s
  * (970 GB/s, P2P over NVLink; profiles/comm_diag_r2.log). */
 int mgb_allgather_results(mgb_ctx* ctx);
+
+/* Minimum of `status` over the ranks of the communicator (ncclAllReduce, min): how the ranks agree that every run succeeded
+ * before they enter mgb_allgather_results together. nranks == 1: *min_status = status. */
+int mgb_comm_agree(mgb_ctx* ctx, int status, int* min_status);
+
+/* ---- level populations on the device ----------------------------------
+ * The level-population half of an ALI iteration (Model::compute_level_populations, model.cpp:654-747) next to the radiation
+ * field, so that an iteration moves nothing across PCIe: J / Lambda are read where the run left them, the per-(point, line)
+ * emissivity / opacity / criterion table the solver reads is rewritten in place. Populations are the reference's long double
+ * values (lineProducingSpecies.hpp:46) carried as double-double pairs: x = hi + lo (lo may be NULL / is 0 for plain doubles).
+ * Block-diagonal statistical equilibrium only (n_off_diag = 0), as Model::compute_level_populations_sparse requires too. */
+typedef struct mgb_lp_convergence { /* LineProducingSpecies::fraction_not_converged, relative_change_mean, relative_change_max */
+    double fraction_not_converged, relative_change_mean, relative_change_max;
+} mgb_lp_convergence;
+/* Parameters::min_line_opacity, min_line_emissivity, population_inversion_fraction, min_rel_pop_for_convergence (parameters.hpp:66-124). */
+int mgb_lp_set_parameters(mgb_ctx* ctx, double min_line_opacity, double min_line_emissivity, double population_inversion_fraction,
+                          double min_rel_pop_for_convergence);
+/* Linedata of line-producing species l (linedata.hpp; Linedata::read, linedata.cpp:12-71): species_index = linedata.num (column of
+ * the abundance table), levels energy / weight [nlev], transitions irad / jrad / frequency / A / Ba / Bs [nrad]. After mgb_set_lines. */
+int mgb_lp_set_species(mgb_ctx* ctx, uint32_t l, uint32_t species_index, uint32_t nlev, uint32_t nrad, const uint32_t* irad,
+                       const uint32_t* jrad, const double* energy, const double* weight, const double* frequency, const double* A,
+                       const double* Ba, const double* Bs);
+/* CollisionPartner (collisionPartner.hpp; read at collisionPartner.cpp:10-45): orth_or_para 0 'n', 1 'o', 2 'p'; Ce, Cd [ntmp][ncol]. */
+int mgb_lp_add_collision_partner(mgb_ctx* ctx, uint32_t l, uint32_t num_col_partner, int orth_or_para, uint32_t ntmp, uint32_t ncol,
+                                 const uint32_t* icol, const uint32_t* jcol, const double* tmp, const double* Ce, const double* Cd);
+/* chemistry.species.abundance [npoints][nspecs]. */
+int mgb_lp_set_abundance(mgb_ctx* ctx, uint32_t nspecs, const double* abundance);
+/* lineProducingSpecies[l].population [npoints][nlev] (+ population_tot [npoints]); seeds the Ng history with it, as
+ * LineProducingSpecies::update_using_LTE does (lineProducingSpecies.tpp:49-69). */
+int mgb_lp_set_populations(mgb_ctx* ctx, uint32_t l, const double* population_hi, const double* population_lo, const double* population_tot);
+int mgb_lp_get_populations(mgb_ctx* ctx, uint32_t l, double* population_hi, double* population_lo);
+/* Lines::set_emissivity_and_opacity + set_inverse_width (lines.tpp:29-59) + InterpHelper criterion (solver_interp_helper.hpp:15-30)
+ * from the device populations into the solver's table; replaces the per-iteration mgb_set_line_state upload. */
+int mgb_lp_refresh_line_state(mgb_ctx* ctx);
+/* The table back on the host: lines.emissivity / opacity / inverse_width [npoints][nlines] (any may be NULL). */
+int mgb_lp_get_line_state(mgb_ctx* ctx, double* emissivity, double* opacity, double* inverse_width);
+/* Model::compute_Jeff (model.cpp:514-545; sparse != 0: compute_Jeff_sparse :549-570, from J per line) for every species, reading
+ * J / Lambda of the last run in place. Needs results for all points (single GPU, or after mgb_allgather_results). */
+int mgb_lp_compute_Jeff(mgb_ctx* ctx, int sparse);
+int mgb_lp_get_Jeff(mgb_ctx* ctx, uint32_t l, double* Jlin, double* Jeff); /* lspec.Jlin / Jeff [npoints][nrad] */
+/* Lines::iteration_using_statistical_equilibrium (lines.cpp:126-137) for every species: population_prev shift and (keep_history != 0)
+ * the Ng history push, LineProducingSpecies::update_using_statistical_equilibrium (lineProducingSpecies.tpp:377-581, one nlev x nlev
+ * block per point), correct_negative_populations (:711-802), check_for_convergence(pop_prec) (:128-165) -> conv [nlspecs],
+ * set_emissivity_and_opacity. ms (may be NULL): device time. A singular block fails with the reference's "Eigen solver ERROR.". */
+int mgb_lp_update_statistical_equilibrium(mgb_ctx* ctx, int keep_history, double pop_prec, mgb_lp_convergence* conv, float* ms);
+/* Ng acceleration, LineProducingSpecies::update_using_acceleration (lineProducingSpecies.tpp:266-314) and _trial (:316-371), split
+ * at the order x order solve, which stays with the host's long double QR: (1) mgb_lp_ng_gram pushes the history entry and returns the
+ * Gram matrix of the last `order` residuals; (2) the host solves RTR c = 1, normalises c; (3) mgb_lp_ng_combine forms the new
+ * population (trial: trial_population) and trims the history like the reference; (4) mgb_lp_finish_update (real step:
+ * correct_negative_populations + check_for_convergence + set_emissivity_and_opacity, lines.cpp:106-117) or
+ * mgb_lp_trial_convergence (check_for_convergence_trial, :171-201). order <= 16. */
+int mgb_lp_ng_gram(mgb_ctx* ctx, uint32_t l, uint32_t order, int trial, double* gram_hi, double* gram_lo);
+int mgb_lp_ng_combine(mgb_ctx* ctx, uint32_t l, uint32_t order, int trial, const double* coef_hi, const double* coef_lo);
+int mgb_lp_finish_update(mgb_ctx* ctx, double pop_prec, mgb_lp_convergence* conv);
+int mgb_lp_trial_convergence(mgb_ctx* ctx, double pop_prec, mgb_lp_convergence* conv);
 
 /* ---- test hooks ------------------------------------------------------------------------------ */
 /* The ray of (origin o, ray pair rr, line l) exactly as Solver::trace_ray_for_line fills nr_/nr_interp_/

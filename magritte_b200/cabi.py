@@ -18,7 +18,10 @@ EXPORTS = [
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
-    "mgb_allgather_results", "mgb_comm_destroy", "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
+    "mgb_allgather_results", "mgb_comm_destroy", "mgb_comm_agree", "mgb_set_radiation_field", "mgb_lp_set_parameters", "mgb_lp_set_species", "mgb_lp_add_collision_partner", "mgb_lp_set_abundance",
+    "mgb_lp_set_populations", "mgb_lp_get_populations", "mgb_lp_refresh_line_state", "mgb_lp_get_line_state", "mgb_lp_compute_Jeff", "mgb_lp_get_Jeff",
+    "mgb_lp_update_statistical_equilibrium", "mgb_lp_ng_gram", "mgb_lp_ng_combine", "mgb_lp_finish_update", "mgb_lp_trial_convergence",
+    "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
 ]
 
 
@@ -295,6 +298,78 @@ class Context:
     def allgather(self):
         self._check(self.lib.mgb_allgather_results(self._ctx), "mgb_allgather_results")
         self.last_range = (0, self.npoints)
+
+    # ---- level populations on the device (mgb_lp_*) ----------------------------------------------
+    def lp_setup(self, species, abundance, parameters=None):
+        """species: the list model.linedata_of / species_from_spec builds; abundance [npoints][nspecs]."""
+        prm = parameters or {}
+        self._check(self.lib.mgb_lp_set_parameters(self._ctx, C.c_double(float(prm.get("min_line_opacity", 1e-13))),
+                                                   C.c_double(float(prm.get("min_line_emissivity", 1e-50))),
+                                                   C.c_double(float(prm.get("population_inversion_fraction", -1.0))),
+                                                   C.c_double(float(prm.get("min_rel_pop_for_convergence", 1e-10)))), "mgb_lp_set_parameters")
+        self.lp_nlev, self.lp_nrad = [], []
+        for l, d in enumerate(species):
+            a = {k: _p(d[k], np.uint32 if k in ("irad", "jrad") else np.float64) for k in ("irad", "jrad", "energy", "weight", "frequency", "A", "Ba", "Bs")}
+            self._check(self.lib.mgb_lp_set_species(self._ctx, C.c_uint32(l), C.c_uint32(int(d["num"])), C.c_uint32(int(d["nlev"])), C.c_uint32(int(d["nrad"])),
+                                                    a["irad"][1], a["jrad"][1], a["energy"][1], a["weight"][1], a["frequency"][1], a["A"][1], a["Ba"][1],
+                                                    a["Bs"][1]), "mgb_lp_set_species")
+            self.lp_nlev.append(int(d["nlev"])); self.lp_nrad.append(int(d["nrad"]))
+            for cp in d["colpar"]:
+                ic, pic = _p(cp["icol"], np.uint32); jc, pjc = _p(cp["jcol"], np.uint32)
+                tm, ptm = _p(cp["tmp"], np.float64); Ce, pCe = _p(cp["Ce"], np.float64); Cd, pCd = _p(cp["Cd"], np.float64)
+                oop = {"n": 0, "o": 1, "p": 2}[str(cp["orth_or_para_H2"])]
+                self._check(self.lib.mgb_lp_add_collision_partner(self._ctx, C.c_uint32(l), C.c_uint32(int(cp["num_col_partner"])), C.c_int(oop),
+                                                                  C.c_uint32(tm.size), C.c_uint32(ic.size), pic, pjc, ptm, pCe, pCd), "mgb_lp_add_collision_partner")
+        ab, pab = _p(abundance, np.float64)
+        self._check(self.lib.mgb_lp_set_abundance(self._ctx, C.c_uint32(ab.shape[1]), pab), "mgb_lp_set_abundance")
+
+    def lp_set_populations(self, l, population, population_tot, lo=None):
+        hi, phi = _p(population, np.float64)
+        plo = None
+        if lo is not None:
+            lo, plo = _p(lo, np.float64)
+        t, pt = _p(population_tot, np.float64)
+        self._check(self.lib.mgb_lp_set_populations(self._ctx, C.c_uint32(l), phi, plo, pt), "mgb_lp_set_populations")
+
+    def lp_get_populations(self, l):
+        hi = np.empty((self.npoints, self.lp_nlev[l])); lo = np.empty_like(hi)
+        self._check(self.lib.mgb_lp_get_populations(self._ctx, C.c_uint32(l), hi.ctypes.data_as(C.c_void_p), lo.ctypes.data_as(C.c_void_p)), "mgb_lp_get_populations")
+        return hi, lo
+
+    def lp_refresh_line_state(self):
+        self._check(self.lib.mgb_lp_refresh_line_state(self._ctx), "mgb_lp_refresh_line_state")
+
+    def lp_get_line_state(self):
+        e, o, w = (np.empty((self.npoints, self.nlines)) for _ in range(3))
+        self._check(self.lib.mgb_lp_get_line_state(self._ctx, *(a.ctypes.data_as(C.c_void_p) for a in (e, o, w))), "mgb_lp_get_line_state")
+        return e, o, w
+
+    def set_radiation_field(self, J, lam_val, lam_cnt, J_lines=None):
+        pj = pjl = None
+        if J is not None:
+            J, pj = _p(J, np.float64)
+        if J_lines is not None:
+            J_lines, pjl = _p(J_lines, np.float64)
+        lv, plv = _p(lam_val, np.float64)
+        lc, plc = _p(lam_cnt, np.uint32)
+        self._check(self.lib.mgb_set_radiation_field(self._ctx, pj, pjl, plv, plc), "mgb_set_radiation_field")
+        self.last_range = (0, self.npoints)
+
+    def lp_compute_Jeff(self, sparse=False):
+        self._check(self.lib.mgb_lp_compute_Jeff(self._ctx, C.c_int(1 if sparse else 0)), "mgb_lp_compute_Jeff")
+
+    def lp_get_Jeff(self, l):
+        a, b = np.empty((self.npoints, self.lp_nrad[l])), np.empty((self.npoints, self.lp_nrad[l]))
+        self._check(self.lib.mgb_lp_get_Jeff(self._ctx, C.c_uint32(l), a.ctypes.data_as(C.c_void_p), b.ctypes.data_as(C.c_void_p)), "mgb_lp_get_Jeff")
+        return a, b
+
+    def lp_update_statistical_equilibrium(self, pop_prec=1e-6, keep_history=False):
+        """-> ([(fraction_not_converged, relative_change_mean, relative_change_max) per species], device ms)"""
+        conv = (C.c_double * (3 * len(self.lp_nlev)))()
+        ms = C.c_float()
+        self._check(self.lib.mgb_lp_update_statistical_equilibrium(self._ctx, C.c_int(1 if keep_history else 0), C.c_double(pop_prec), conv, C.byref(ms)),
+                    "mgb_lp_update_statistical_equilibrium")
+        return [tuple(conv[3 * l:3 * l + 3]) for l in range(len(self.lp_nlev))], ms.value
 
     # ---- test hooks -------------------------------------------------------------------------
     def trace(self, o, rr, l, cap=4096):

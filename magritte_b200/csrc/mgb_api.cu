@@ -14,6 +14,7 @@ static std::string g_create_error;
 
 mgb_ctx::~mgb_ctx() {
     drop_chunks();
+    for (auto* s : lp) delete s;
     if (ev_a) cudaEventDestroy(ev_a);
     if (ev_b) cudaEventDestroy(ev_b);
     if (stream) cudaStreamDestroy(stream);
@@ -653,6 +654,24 @@ extern "C" int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, do
     const size_t L = ctx->m.nlines, n = (size_t)(o_end - o_begin) * L;
     MGB_CUDA(ctx, cudaMemcpy(lambda_val, ctx->lam_val.as<double>() + (size_t)o_begin * L, 8 * n, cudaMemcpyDeviceToHost));
     MGB_CUDA(ctx, cudaMemcpy(lambda_cnt, ctx->lam_cnt.as<uint32_t>() + (size_t)o_begin * L, 4 * n, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+// A radiation field computed elsewhere (another run, a checkpoint, the reference) as the result of the "last run": what
+// mgb_lp_compute_Jeff and the getters then see. Any of J / J_lines may be NULL (left as it is).
+extern "C" int mgb_set_radiation_field(mgb_ctx* ctx, const double* J, const double* J_lines, const double* lambda_val, const uint32_t* lambda_cnt) {
+    if (!ctx || !lambda_val || !lambda_cnt) return MGB_EINVAL;
+    if (!(ctx->have_geometry && ctx->have_lines && ctx->have_freqs)) return ctx->fail(MGB_ESTATE, "mgb_set_radiation_field: geometry / lines / frequencies not set");
+    cudaSetDevice(ctx->device);
+    MGB_TRY(mgb_internal_alloc_results(ctx));
+    const DevModel& m = ctx->m;
+    const size_t N = m.npoints;
+    if (J) MGB_CUDA(ctx, cudaMemcpyAsync(ctx->J.p, J, 8 * N * m.nfreqs, cudaMemcpyHostToDevice, ctx->stream));
+    if (J_lines) MGB_CUDA(ctx, cudaMemcpyAsync(ctx->J_lines.p, J_lines, 8 * N * m.nlines, cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, cudaMemcpyAsync(ctx->lam_val.p, lambda_val, 8 * N * m.nlines, cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, cudaMemcpyAsync(ctx->lam_cnt.p, lambda_cnt, 4 * N * m.nlines, cudaMemcpyHostToDevice, ctx->stream));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->res_o0 = 0; ctx->res_o1 = m.npoints; ctx->res_K = 0; ctx->lam_cap = 1; ctx->res_valid = true;
     return MGB_OK;
 }
 

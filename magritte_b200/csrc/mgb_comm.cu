@@ -20,6 +20,7 @@ struct Nccl {
     ncclResult_t (*CommDestroy)(ncclComm_t)                                                      = nullptr;
     ncclResult_t (*AllGather)(const void*, void*, size_t, int, ncclComm_t, cudaStream_t)         = nullptr;
     ncclResult_t (*Broadcast)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t)    = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t)    = nullptr;
     ncclResult_t (*GroupStart)()                                                                 = nullptr;
     ncclResult_t (*GroupEnd)()                                                                   = nullptr;
     const char* (*GetErrorString)(ncclResult_t)                                                  = nullptr;
@@ -31,7 +32,7 @@ struct Nccl {
         *(void**)(&f) = dlsym(h, name);                            \
         if (!f) { err = std::string("dlsym ") + name; return false; }
         SYM(GetUniqueId, "ncclGetUniqueId") SYM(CommInitRank, "ncclCommInitRank") SYM(CommDestroy, "ncclCommDestroy")
-        SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
+        SYM(AllGather, "ncclAllGather") SYM(Broadcast, "ncclBroadcast") SYM(AllReduce, "ncclAllReduce") SYM(GroupStart, "ncclGroupStart") SYM(GroupEnd, "ncclGroupEnd")
         SYM(GetErrorString, "ncclGetErrorString")
 #undef SYM
         return true;
@@ -73,6 +74,22 @@ extern "C" int mgb_comm_destroy(mgb_ctx* ctx) {
     }
     ctx->comm = nullptr; ctx->nranks = 1; ctx->rank = 0;
     ctx->part_bounds.clear();
+    return MGB_OK;
+}
+
+extern "C" int mgb_comm_agree(mgb_ctx* ctx, int status, int* min_status) {
+    if (!ctx || !min_status) return MGB_EINVAL;
+    *min_status = status;
+    if (ctx->nranks == 1) return MGB_OK;
+    if (!ctx->comm) return ctx->fail(MGB_ESTATE, "mgb_comm_agree: mgb_comm_init was not called");
+    cudaSetDevice(ctx->device);
+    MGB_CUDA(ctx, ctx->counters.ensure(64));
+    int* d = reinterpret_cast<int*>(ctx->counters.as<unsigned long long>() + 7);
+    MGB_CUDA(ctx, cudaMemcpyAsync(d, &status, 4, cudaMemcpyHostToDevice, ctx->stream));
+    const ncclResult_t r = g_nccl.AllReduce(d, d, 1, /* ncclInt32 */ 2, /* ncclMin */ 3, (ncclComm_t)ctx->comm, ctx->stream);
+    if (r) return ctx->fail(MGB_ENCCL, "ncclAllReduce: %s", g_nccl.GetErrorString(r));
+    MGB_CUDA(ctx, cudaMemcpyAsync(min_status, d, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return MGB_OK;
 }
 

@@ -43,6 +43,28 @@ struct PathChunk {
     DevBuf poff, nr, dZ, shift, shift0;
 };
 
+// ---- level populations on the device (mgb_levelpop.cu) ----
+struct LpColPar { // CollisionPartner (reference linedata/collisionPartner/collisionPartner.hpp)
+    uint32_t num_col_partner = 0, orth_or_para = 0 /* 0 'n', 1 'o', 2 'p' */, ntmp = 0, ncol = 0;
+    DevBuf icol, jcol, tmp, Ce, Cd; // Ce, Cd [ntmp][ncol]
+};
+struct LpSpecies { // LineProducingSpecies + Linedata (lineProducingSpecies.hpp, linedata.hpp)
+    uint32_t nlev = 0, nrad = 0, num = 0, line0 = 0;
+    bool have_pop = false;
+    DevBuf irad, jrad, energy, weight, frequency, A, Ba, Bs;
+    std::vector<LpColPar*> colpar;
+    DevBuf colpar_views;
+    DevBuf pop, prev1, prev2, prev3, trial, trial_prev; // double2 {hi, lo} [npoints][nlev]: the reference's long double populations
+    std::vector<DevBuf*> populations, residuals;         // Ng history (lineProducingSpecies.hpp:56-57)
+    DevBuf Jlin, Jeff, Jdif;                             // [npoints][nrad]
+    DevBuf pop_tot;                                      // [npoints]
+    ~LpSpecies() {
+        for (auto* c : colpar) delete c;
+        for (auto* b : populations) delete b;
+        for (auto* b : residuals) delete b;
+    }
+};
+
 } // namespace mgb
 
 struct mgb_ctx {
@@ -93,6 +115,12 @@ struct mgb_ctx {
     double h_pos_p2b0[3] = {0, 0, 0}; // position[point2boundary[0]] when that is a valid point index
     double h_pos_last[3] = {0, 0, 0}; // position[npoints-1] (start point of a spherically symmetric image)
     mgb::DevBuf im_X, im_Y, im_len, im_start, im_shift0, im_poff, im_nr, im_nri, im_fac, im_sh, im_dz, im_I, im_nu;
+    // level populations on the device
+    std::vector<mgb::LpSpecies*> lp;
+    mgb::DevBuf lp_abundance, lp_partials, lp_flags;
+    uint32_t lp_nspecs = 0;
+    double lp_min_line_opacity = 1.0e-13, lp_min_line_emissivity = 1.0e-50, lp_population_inversion_fraction = -1.0,
+           lp_min_rel_pop_for_convergence = 1.0e-10;
     // NCCL
     void* comm = nullptr;
     int nranks = 1, rank = 0;

@@ -56,6 +56,21 @@ PYBIND11_MODULE(core, m) {
     py::class_<Model>(m, "Model")
         .def(py::init<>())
         .def_readwrite("device", &Model::device)
+        .def_readwrite("device_level_populations", &Model::device_level_populations)
+        .def_readonly("nranks", &Model::nranks)
+        .def_readonly("rank", &Model::rank)
+        .def_readonly("o_begin", &Model::o_begin)
+        .def_readonly("o_end", &Model::o_end)
+        .def_static("nccl_unique_id", []() { return py::bytes(Model::nccl_unique_id()); })
+        .def("set_communicator", [](Model& s, int nranks, int rank, py::bytes id) { s.set_communicator(nranks, rank, std::string(id)); })
+        .def_property_readonly("last_stats", [](const Model& s) {
+            py::dict d;
+            d["n_steps"] = s.last_stats.n_steps; d["n_entries"] = s.last_stats.n_entries; d["n_solves"] = s.last_stats.n_solves;
+            d["n_launches"] = s.last_stats.n_launches; d["ms_solve"] = s.last_stats.ms_solve; d["ms_total"] = s.last_stats.ms_total;
+            d["ms_trace_count"] = s.last_stats.ms_trace_count; d["ms_trace_fill"] = s.last_stats.ms_trace_fill; d["ms_reduce"] = s.last_stats.ms_reduce;
+            d["n_solve_launches"] = s.last_stats.n_solve_launches; d["paths_cached"] = s.last_stats.paths_cached;
+            return d;
+        })
         .def_readonly("parameters", &Model::parameters, py::return_value_policy::reference_internal)
         .def_readonly("images", &Model::images)
         .def_readonly("error_mean", &Model::error_mean)

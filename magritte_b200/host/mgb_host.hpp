@@ -458,6 +458,26 @@ class Model {
     Model& operator=(const Model&) = delete;
     ~Model() { if (ctx) mgb_destroy(ctx); }
 
+    // ---- B200 knobs (no reference counterpart) ----
+    // true (default): statistical equilibrium, Ng acceleration, compute_Jeff and the emissivity/opacity refresh of
+    // compute_level_populations[_sparse] run on the GPU (mgb_lp_*), an iteration moves nothing across PCIe; false: the host twin
+    // below (long double, the reference's code path), with the line state uploaded and J / Lambda downloaded every iteration.
+    bool device_level_populations = true;
+    // One process per GPU: origins are partitioned over the ranks (cost-balanced), J / Lambda slices all-gathered over NCCL before
+    // the level-population update (replaces Radiation::MPI_reduce_J / Lambda::MPI_gather, solver.tpp:530-539). id128 from
+    // nccl_unique_id() of rank 0, distributed by the application.
+    static std::string nccl_unique_id() {
+        std::string id(128, '\0');
+        if (mgb_nccl_unique_id(&id[0]) != MGB_OK) throw std::runtime_error("mgb_nccl_unique_id failed (libnccl.so.2 not loadable?)");
+        return id;
+    }
+    void set_communicator(const int nranks_, const int rank_, const std::string& id128) {
+        if (nranks_ < 1 || rank_ < 0 || rank_ >= nranks_ || id128.size() != 128) throw std::runtime_error("set_communicator: bad arguments");
+        nranks = nranks_; rank = rank_; comm_id = id128; comm_dirty = true;
+    }
+    int nranks = 1, rank = 0;
+    Size o_begin = 0, o_end = 0; // this rank's origins in the last radiation-field call
+
     Size nlines() const { Size n = 0; for (auto& l : lineProducingSpecies) n += l.linedata.nrad; return n; }
     Size nlspecs() const { return (Size)lineProducingSpecies.size(); }
     Size nquads() const { return lineProducingSpecies.empty() ? 0 : (Size)lineProducingSpecies[0].quadrature_roots.size(); }
@@ -586,15 +606,13 @@ class Model {
             throw std::runtime_error("magritte_b200.core: n_off_diag > 0 couples the rate equations of neighbouring points (one global sparse system, "
                                      "lineProducingSpecies.tpp:377-581); the host layer solves the block-diagonal case only. The banded Lambda "
                                      "lists are available from the C ABI (mgb_get_lambda_lists).");
-        sync_static(true);
+        run_radiation_field(true);
         const Size L = nlines();
         J.resize((size_t)npoints * nfreqs);
         std::vector<double> lam((size_t)npoints * L);
         std::vector<uint32_t> cnt((size_t)npoints * L);
-        std::vector<double> ptot((size_t)nlspecs() * npoints);
-        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
-        check(mgb_solve_feautrier_order_2(ctx, approx(), emissivity.data(), opacity.data(), inverse_width.data(), ptot.data(), 0, npoints,
-                                          J.data(), lam.data(), cnt.data(), nullptr, &last_stats), "mgb_solve_feautrier_order_2");
+        check(mgb_get_J(ctx, 0, npoints, J.data()), "mgb_get_J");
+        check(mgb_get_lambda(ctx, 0, npoints, lam.data(), cnt.data()), "mgb_get_lambda");
         for (Size l = 0; l < nlspecs(); l++) { /* Lambda lists per species: lambda.Ls[p][k], nr == p */
             auto& ls = lineProducingSpecies[l];
             const Size nrad = ls.linedata.nrad;
@@ -610,14 +628,10 @@ class Model {
     //      solver.tpp:297-363): the same solves, but only J integrated over each line (lspec.J) and Lambda leave the device ----
     int compute_radiation_field_feautrier_order_2_sparse() {
         if (parameters.n_off_diag) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update.");
-        sync_static(true);
+        run_radiation_field(true);
         const Size L = nlines();
         std::vector<double> jl((size_t)npoints * L), lam((size_t)npoints * L);
         std::vector<uint32_t> cnt((size_t)npoints * L);
-        std::vector<double> ptot((size_t)nlspecs() * npoints);
-        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
-        check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
-        check(mgb_run_feautrier_order_2(ctx, approx(), 0, npoints, &last_stats), "mgb_run_feautrier_order_2");
         check(mgb_get_J_lines(ctx, 0, npoints, jl.data()), "mgb_get_J_lines");
         check(mgb_get_lambda(ctx, 0, npoints, lam.data(), cnt.data()), "mgb_get_lambda");
         for (Size l = 0; l < nlspecs(); l++) {
@@ -733,6 +747,7 @@ class Model {
     int compute_level_populations_sparse(const bool use_Ng_acceleration, const long max_niterations) { return level_population_loop(use_Ng_acceleration, max_niterations, true); }
     int level_population_loop(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
         if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
+        if (device_level_populations) return level_population_loop_device(use_Ng_acceleration, max_niterations, sparse);
         int iteration = 0, iteration_normal = 0;
         error_mean.clear(); error_max.clear();
         bool some_not_converged = true;
@@ -761,6 +776,84 @@ class Model {
         }
         return iteration;
     }
+    // ---- the same loop with the level-population half on the GPU (mgb_lp_*, magritte_b200/csrc/mgb_levelpop.cu) ----
+    // Control flow is Model::compute_level_populations[_sparse] (model.cpp:655-748, 756-850) and ng_acceleration_criterion (:580-653)
+    // unchanged; each step calls the device twin of the Lines:: / LineProducingSpecies:: routine the reference calls. Host copies of
+    // populations, Jlin/Jeff, the line state, J (or lspec.J) and Lambda are refreshed when the loop ends.
+    int level_population_loop_device(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
+        if (parameters.n_off_diag) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update."); /* block-diagonal only */
+        sync_static(true);
+        sync_levelpop();
+        int iteration = 0, iteration_normal = 0;
+        error_mean.clear(); error_max.clear();
+        bool some_not_converged = true;
+        std::vector<mgb_lp_convergence> conv(nlspecs());
+        auto store_conv = [&]() {
+            for (Size l = 0; l < nlspecs(); l++) {
+                lineProducingSpecies[l].fraction_not_converged = conv[l].fraction_not_converged;
+                lineProducingSpecies[l].relative_change_mean   = conv[l].relative_change_mean;
+                lineProducingSpecies[l].relative_change_max    = conv[l].relative_change_max;
+            }
+        };
+        auto sum_fnc = [&]() {
+            double s = 0.0;
+            for (auto& l : lineProducingSpecies) s += parameters.adaptive_Ng_acceleration_use_max_criterion ? l.relative_change_max : l.relative_change_mean;
+            return s;
+        };
+        auto ng_step = [&](const Size order, const bool trial) { /* update_using_acceleration[_trial] for every species */
+            for (Size l = 0; l < nlspecs(); l++) {
+                std::vector<double> ghi((size_t)order * order), glo((size_t)order * order);
+                check(mgb_lp_ng_gram(ctx, l, order, trial ? 1 : 0, ghi.data(), glo.data()), "mgb_lp_ng_gram");
+                std::vector<LD> RTR((size_t)order * order);
+                for (size_t i = 0; i < RTR.size(); i++) RTR[i] = (LD)ghi[i] + (LD)glo[i];
+                VecLD coef = colpiv_qr_solve(RTR, VecLD(order, 1.0L), order);
+                LD sum = 0; for (LD c : coef) sum += c;
+                std::vector<double> chi(order), clo(order);
+                for (Size i = 0; i < order; i++) { const LD c = coef[i] / sum; chi[i] = (double)c; clo[i] = (double)(c - (LD)chi[i]); }
+                check(mgb_lp_ng_combine(ctx, l, order, trial ? 1 : 0, chi.data(), clo.data()), "mgb_lp_ng_combine");
+            }
+        };
+        while (some_not_converged && (iteration < max_niterations)) {
+            bool do_ng = false; Size order = 0;
+            const Size skip_N_its = parameters.Ng_acceleration_remove_N_its, prior = (Size)iteration_normal;
+            if (!parameters.use_adaptive_Ng_acceleration) {
+                if (use_Ng_acceleration && prior == parameters.Ng_acceleration_mem_limit + skip_N_its) { do_ng = true; order = parameters.Ng_acceleration_mem_limit; }
+            } else if (use_Ng_acceleration && prior >= parameters.adaptive_Ng_acceleration_min_order + skip_N_its) {
+                const double sum_fnc_curr = sum_fnc();
+                ng_step(prior - skip_N_its, true);
+                check(mgb_lp_trial_convergence(ctx, parameters.pop_prec, conv.data()), "mgb_lp_trial_convergence");
+                store_conv();
+                const double sum_fnc_ng = sum_fnc();
+                if ((sum_fnc_ng < sum_fnc_curr) || prior == (parameters.Ng_acceleration_mem_limit + skip_N_its)) { do_ng = true; order = prior - skip_N_its; }
+            }
+            if (do_ng) {
+                ng_step(order, false);
+                check(mgb_lp_finish_update(ctx, parameters.pop_prec, conv.data()), "mgb_lp_finish_update");
+                store_conv();
+                iteration_normal = 0;
+            } else {
+                iteration++;
+                some_not_converged = false;
+                const double t0 = now();
+                run_radiation_field(false);
+                check(mgb_lp_compute_Jeff(ctx, sparse ? 1 : 0), "mgb_lp_compute_Jeff");
+                const double t1 = now();
+                check(mgb_lp_update_statistical_equilibrium(ctx, use_Ng_acceleration ? 1 : 0, parameters.pop_prec, conv.data(), nullptr), "mgb_lp_update_statistical_equilibrium");
+                store_conv();
+                const double t2 = now();
+                seconds_radiation_field += t1 - t0; seconds_statistical_equilibrium += t2 - t1;
+                iteration_normal++;
+                for (auto& l : lineProducingSpecies) {
+                    error_mean.push_back(l.relative_change_mean);
+                    error_max.push_back(l.relative_change_max);
+                    if (l.fraction_not_converged > 1.0 - parameters.convergence_fraction) some_not_converged = true;
+                }
+            }
+        }
+        download_levelpop(sparse);
+        return iteration;
+    }
+
     // ---- Model::compute_image_new(rx, ry, rz, Nxpix, Nypix) (model.cpp:999-1035) ----
     int compute_image_new(const double rx, const double ry, const double rz, const Size Nxpix, const Size Nypix) { return image_new(false, rx, ry, rz, Nxpix, Nypix); }
     // ---- Model::compute_image_optical_depth_new(raydir, Nxpix, Nypix) (model.cpp:1102-1127): Image.I holds optical depths ----
@@ -812,7 +905,93 @@ class Model {
 
   private:
     mgb_ctx* ctx = nullptr;
-    bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true;
+    bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true, dirty_species = true, comm_dirty = false;
+    std::string comm_id;
+    bool have_partition = false;
+    // One radiation-field pass on this rank's origins (+ the all-gather): Solver::solve_feautrier_order_2[_sparse] (solver.tpp:297-363, 458-540).
+    // upload_state: the host's emissivity / opacity / inverse_width go up first (the host-twin path); otherwise the device table is current.
+    void run_radiation_field(const bool upload_state) {
+        sync_static(true);
+        if (upload_state) {
+            std::vector<double> ptot((size_t)nlspecs() * npoints);
+            for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
+            check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+        }
+        if (nranks == 1) { o_begin = 0; o_end = npoints; }
+        else if (!have_partition) {
+            check(mgb_partition_balanced(ctx, nranks, rank, &o_begin, &o_end), "mgb_partition_balanced");
+            have_partition = true;
+        }
+        const int rc = mgb_run_feautrier_order_2(ctx, approx(), o_begin, o_end, &last_stats);
+        if (nranks > 1) { /* agree before the collective: a rank that failed must not leave its peers inside the all-gather */
+            int all = rc;
+            check(mgb_comm_agree(ctx, rc, &all), "mgb_comm_agree");
+            check(rc, "mgb_run_feautrier_order_2");
+            if (all != MGB_OK) throw std::runtime_error("mgb_run_feautrier_order_2 failed on another rank (" + std::to_string(all) + ")");
+            check(mgb_allgather_results(ctx), "mgb_allgather_results");
+        } else check(rc, "mgb_run_feautrier_order_2");
+    }
+    static void split_ld(const VecLD& v, std::vector<double>& hi, std::vector<double>& lo) {
+        hi.resize(v.size()); lo.resize(v.size());
+        for (size_t i = 0; i < v.size(); i++) { hi[i] = (double)v[i]; lo[i] = (double)(v[i] - (LD)hi[i]); }
+    }
+    // Static level-population inputs (once) and the current host populations + line state (every loop start: the host may have set them).
+    void sync_levelpop() {
+        if (dirty_species) {
+            check(mgb_lp_set_parameters(ctx, (double)parameters.min_line_opacity, (double)parameters.min_line_emissivity,
+                                        parameters.population_inversion_fraction, parameters.min_rel_pop_for_convergence), "mgb_lp_set_parameters");
+            for (Size l = 0; l < nlspecs(); l++) {
+                const Linedata& ld = lineProducingSpecies[l].linedata;
+                check(mgb_lp_set_species(ctx, l, ld.num, ld.nlev, ld.nrad, ld.irad.data(), ld.jrad.data(), ld.energy.data(), ld.weight.data(),
+                                         ld.frequency.data(), ld.A.data(), ld.Ba.data(), ld.Bs.data()), "mgb_lp_set_species");
+                for (const CollisionPartner& cp : ld.colpar) {
+                    const Size ntmp = (Size)cp.tmp.size(), ncol = (Size)cp.icol.size();
+                    std::vector<double> Ce((size_t)ntmp * ncol), Cd((size_t)ntmp * ncol);
+                    for (Size t = 0; t < ntmp; t++) { std::copy(cp.Ce[t].begin(), cp.Ce[t].end(), Ce.begin() + (size_t)t * ncol); std::copy(cp.Cd[t].begin(), cp.Cd[t].end(), Cd.begin() + (size_t)t * ncol); }
+                    const int oop = cp.orth_or_para_H2 == "o" ? 1 : (cp.orth_or_para_H2 == "p" ? 2 : 0);
+                    check(mgb_lp_add_collision_partner(ctx, l, cp.num_col_partner, oop, ntmp, ncol, cp.icol.data(), cp.jcol.data(), cp.tmp.data(), Ce.data(), Cd.data()),
+                          "mgb_lp_add_collision_partner");
+                }
+            }
+            check(mgb_lp_set_abundance(ctx, nspecs, abundance.data()), "mgb_lp_set_abundance");
+            dirty_species = false;
+        }
+        std::vector<double> hi, lo;
+        for (Size l = 0; l < nlspecs(); l++) {
+            split_ld(lineProducingSpecies[l].population, hi, lo);
+            check(mgb_lp_set_populations(ctx, l, hi.data(), lo.data(), lineProducingSpecies[l].population_tot.data()), "mgb_lp_set_populations");
+        }
+        std::vector<double> ptot((size_t)nlspecs() * npoints);
+        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
+        check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+    }
+    void download_levelpop(const bool sparse) {
+        const Size L = nlines();
+        std::vector<double> hi, lo;
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& ls = lineProducingSpecies[l];
+            hi.resize(ls.population.size()); lo.resize(ls.population.size());
+            check(mgb_lp_get_populations(ctx, l, hi.data(), lo.data()), "mgb_lp_get_populations");
+            for (size_t i = 0; i < hi.size(); i++) ls.population[i] = (LD)hi[i] + (LD)lo[i];
+            check(mgb_lp_get_Jeff(ctx, l, ls.Jlin.data(), ls.Jeff.data()), "mgb_lp_get_Jeff");
+        }
+        check(mgb_lp_get_line_state(ctx, emissivity.data(), opacity.data(), nullptr), "mgb_lp_get_line_state");
+        std::vector<double> jl((size_t)npoints * L), lam((size_t)npoints * L);
+        std::vector<uint32_t> cnt((size_t)npoints * L);
+        if (!sparse) { J.resize((size_t)npoints * nfreqs); check(mgb_get_J(ctx, 0, npoints, J.data()), "mgb_get_J"); }
+        check(mgb_get_J_lines(ctx, 0, npoints, jl.data()), "mgb_get_J_lines");
+        check(mgb_get_lambda(ctx, 0, npoints, lam.data(), cnt.data()), "mgb_get_lambda");
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& ls = lineProducingSpecies[l];
+            const Size nrad = ls.linedata.nrad;
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    if (sparse) ls.J[(size_t)p * nrad + k] = jl[(size_t)p * L + nrad_cum[l] + k];
+                    ls.lambda_Ls[(size_t)p * nrad + k]  = lam[(size_t)p * L + nrad_cum[l] + k];
+                    ls.lambda_cnt[(size_t)p * nrad + k] = cnt[(size_t)p * L + nrad_cum[l] + k];
+                }
+        }
+    }
     static double now() { timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec + 1e-9 * ts.tv_nsec; }
     void check(int rc, const char* what) {
         if (rc != MGB_OK) throw std::runtime_error(std::string(what) + " failed (" + std::to_string(rc) + "): " + mgb_last_error(ctx));
@@ -833,7 +1012,7 @@ class Model {
             check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
                                    direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
                                    boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
-            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true;
+            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true; have_partition = false;
         }
         if (dirty_thermo) { check(mgb_set_thermodynamics(ctx, temperature_gas.data(), vturb2.data()), "mgb_set_thermodynamics"); dirty_thermo = false; }
         if (dirty_lines) {
@@ -844,7 +1023,11 @@ class Model {
                 qw.insert(qw.end(), l.quadrature_weights.begin(), l.quadrature_weights.end());
             }
             check(mgb_set_lines(ctx, nlspecs(), nrad.data(), im.data(), line.data(), A.data(), nquads(), qw.data()), "mgb_set_lines");
-            dirty_lines = false; dirty_freqs = true;
+            dirty_lines = false; dirty_freqs = true; dirty_species = true;
+        }
+        if (comm_dirty) {
+            check(mgb_comm_init(ctx, nranks, rank, comm_id.data()), "mgb_comm_init");
+            comm_dirty = false; have_partition = false;
         }
         if (need_line_freqs) {
             if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/magritte_b200.h but not exported"
     assert sorted(cabi.EXPORTS) == names
-    assert lib.mgb_abi_version() == 1
+    assert lib.mgb_abi_version() == 2
 
 
 def test_no_cpu_fallback():

@@ -21,6 +21,7 @@ def prepared(name):
 @pytest.mark.parametrize("name", CASES)
 def test_K_iterations_without_Ng(name):
     m, flat, ref, lp = prepared(name)
+    m.device_level_populations = False  # the host twin (long double); the device path: tests/test_gpu_levelpop_device.py
     m.mutable_parameters().use_adaptive_Ng_acceleration = False
     it = m.compute_level_populations(False, lp["K"])
     assert it == lp["K"]
@@ -35,6 +36,7 @@ def test_K_iterations_without_Ng(name):
 @pytest.mark.parametrize("name", ["c1_all_constant", "c2_vanzadelhoff", "wind3d_small"])
 def test_default_adaptive_Ng_run(name):
     m, flat, ref, lp = prepared(name)
+    m.device_level_populations = False
     it = m.compute_level_populations(True, 60)
     assert it == lp["Ng_iterations"]
     for l, want in enumerate(lp["Ng_population"]):

@@ -77,6 +77,7 @@ def test_K_sparse_iterations_without_Ng(name):
 def test_default_adaptive_Ng_sparse_run(name):
     m, flat, ref, lp = prepared(name)
     sp = load_sparse(name)
+    m.device_level_populations = False
     it = m.compute_level_populations_sparse(True, 60)
     # Where the QR noise floor decides convergence the count is the solver's, not the method's: the reference's own sparse run of
     # wind3d_small stalls at error_max ~ 1e-5 and needs 7 iterations where its dense run needs 4 (tests/golden/levelpop_*.pkl).
