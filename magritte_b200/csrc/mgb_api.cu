@@ -1,12 +1,13 @@
 // mgb_api.cu -- C ABI of libmagritte_b200.so: context, model upload, the Feautrier order-2 run, result download.
 // See include/magritte_b200.h for the contract and the reference citations of every entry point.
 #include <algorithm>
+#include <cstdlib>
 #include <numeric>
 
 #include <cub/device/device_scan.cuh>
 
 #include "mgb_ctx.h"
-#include "mgb_solve.cuh"
+#include "mgb_solve2.cuh"
 
 using namespace mgb;
 
@@ -257,9 +258,26 @@ static int build_freq_chunks(mgb_ctx* ctx) {
         f0 = f1;
     }
     MGB_TRY(upload(ctx, ctx->freq_chunks, ch.data(), sizeof(FreqChunk) * ch.size()));
+    // k_solve2: whole lines per warp, two bins of one line per lane (lane = k * lpl + j owns bins z0+j and z0+j+lpl of line l0+k)
+    std::vector<FreqChunk2> ch2;
+    uint32_t lpw2 = 1;
+    if (nq <= 64) {
+        const uint32_t lpl = (nq + 1) / 2;
+        lpw2 = std::max(1u, std::min(std::min(32u / lpl, 8u), ctx->m.nlines));
+        for (uint32_t l0 = 0; l0 < ctx->m.nlines; l0 += lpw2) ch2.push_back(FreqChunk2{l0, std::min(lpw2, ctx->m.nlines - l0), 0, nq, lpl});
+    } else {
+        for (uint32_t l = 0; l < ctx->m.nlines; l++)
+            for (uint32_t z0 = 0; z0 < nq; z0 += 64) {
+                const uint32_t nz = std::min(64u, nq - z0);
+                ch2.push_back(FreqChunk2{l, 1, z0, nz, (nz + 1) / 2});
+            }
+    }
+    MGB_TRY(upload(ctx, ctx->freq_chunks2, ch2.data(), sizeof(FreqChunk2) * ch2.size()));
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     ctx->n_freq_chunks = (uint32_t)ch.size();
     ctx->lines_per_warp = lpw;
+    ctx->n_freq_chunks2 = (uint32_t)ch2.size();
+    ctx->lines_per_warp2 = lpw2;
     return MGB_OK;
 }
 
@@ -411,9 +429,31 @@ cudaError_t launch_solve2(mgb_ctx* ctx, const PathView& pv, const ScratchView& s
                                                                         ctx->lines_per_warp);
     return cudaGetLastError();
 }
+// n_off_diag = 0: the solve kernel leaves L_diag in sc.L and k_reduce_lambda2 applies the origin's factors. MGB_SOLVE_V2=1 in the environment
+// selects k_solve2 (mgb_solve2.cuh: two bins per lane, straight-line common step; bit-identical, measured SLOWER on B200 -- see DESIGN.md 6).
+template <int APPROX>
+cudaError_t launch_solve_v2(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc) {
+    const size_t nitems = (size_t)pv.no * ctx->m.hnrays * ctx->n_freq_chunks2;
+    const size_t blocks = (nitems + kSolve2Warps - 1) / kSolve2Warps;
+    const size_t smem   = kSolve2Warps * solve2_smem_per_warp(ctx->lines_per_warp2);
+    cudaError_t e = cudaFuncSetAttribute(k_solve2<APPROX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_solve2<APPROX><<<(unsigned)blocks, 32 * kSolve2Warps, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks2.as<FreqChunk2>(), ctx->n_freq_chunks2,
+                                                                               ctx->lines_per_warp2);
+    return cudaGetLastError();
+}
 template <int APPROX>
 cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
-    return sc.K ? launch_solve2<APPROX, true>(ctx, pv, sc, nchunks_f) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
+    if (sc.K) return launch_solve2<APPROX, true>(ctx, pv, sc, nchunks_f);
+    return ctx->solve_v2 ? launch_solve_v2<APPROX>(ctx, pv, sc) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
+}
+template <int APPROX>
+cudaError_t launch_reduce_lambda2(mgb_ctx* ctx, uint32_t o0, uint32_t no, const ScratchView& sc) {
+    const size_t nl = (size_t)no * ctx->m.nlines;
+    k_reduce_lambda2<APPROX><<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(ctx->m, o0, no, ctx->lens.as<uint32_t>(), sc.L, ctx->lam_val.as<double>(),
+                                                                                   ctx->lam_cnt.as<uint32_t>(), ctx->scratch_fac.as<double>(),
+                                                                                   ctx->scratch_fac.as<double>() + (size_t)no * ctx->m.nfreqs);
+    return cudaGetLastError();
 }
 
 } // namespace
@@ -558,6 +598,12 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     MGB_CUDA(ctx, ctx->scratch_L.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
     MGB_CUDA(ctx, ctx->counters.ensure(64));
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
+    {
+        const char* v2 = getenv("MGB_SOLVE_V2");
+        ctx->solve_v2 = v2 && v2[0] == '1';
+    }
+    const bool lambda2 = !K; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
+    if (lambda2) MGB_CUDA(ctx, ctx->scratch_fac.ensure(16 * (size_t)max_no * m.nfreqs));
     if (K) { /* banded operator: at most 1 + 2K distinct points per ray pair (lambda.tpp:79-89 lists) */
         ctx->lam_cap = 1 + 2 * K * m.hnrays;
         MGB_CUDA(ctx, ctx->lam_list_val.ensure(8 * prow * m.nlines * ctx->lam_cap));
@@ -597,7 +643,11 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
             k_reduce_lambda_banded<<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(
                 m, ch->o0, no, K, ctx->lam_cap, ctx->lens.as<uint32_t>(), sc.L, sc.offV, sc.offN, ctx->lam_list_val.as<double>(),
                 ctx->lam_list_nr.as<uint32_t>(), ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>(), ctx->counters.as<unsigned long long>() + 4);
-        else
+        else if (lambda2) {
+            if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_reduce_lambda2<APPROX_NONE>(ctx, ch->o0, no, sc));
+            else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_reduce_lambda2<APPROX_ONELINE>(ctx, ch->o0, no, sc));
+            else MGB_CUDA(ctx, launch_reduce_lambda2<APPROX_CLOSELINES>(ctx, ch->o0, no, sc));
+        } else
             k_reduce_lambda<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.L,
                                                                                    ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
         MGB_CUDA(ctx, cudaGetLastError());

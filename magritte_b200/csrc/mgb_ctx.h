@@ -80,11 +80,13 @@ struct mgb_ctx {
     std::vector<double> inverse_mass;
     double max_inverse_mass = 0.0;
     uint32_t n_freq_chunks = 0, lines_per_warp = 1; // k_solve work decomposition (build_freq_chunks)
+    uint32_t n_freq_chunks2 = 0, lines_per_warp2 = 1; // k_solve2: whole lines per warp, two bins per lane
+    bool solve_v2 = false;                            // MGB_SOLVE_V2=1: k_solve2 instead of k_solve for n_off_diag = 0
     mgb::DevModel m{};
     // device storage
     mgb::DevBuf pos, vel, csr, nbs, dir, weight, antipod, p2b, bcond, btemp;
     mgb::DevBuf temperature, vturb2, sqrtw_max, dshift_max, inv_mass_dev;
-    mgb::DevBuf lrow, line, sorted_line, sorted_map, sorted_pos, freq_chunks, line_A, line_invmass, line_k_dev, line_spec_dev, line_quadw;
+    mgb::DevBuf lrow, line, sorted_line, sorted_map, sorted_pos, freq_chunks, freq_chunks2, line_A, line_invmass, line_k_dev, line_spec_dev, line_quadw;
     mgb::DevBuf nu, corr_line;
     mgb::DevBuf stage_a, stage_b, stage_c, stage_d; // H2D staging of the per-iteration line state
     // results
@@ -105,7 +107,7 @@ struct mgb_ctx {
     uint32_t plan_o0 = 0, plan_o1 = 0;
     bool plan_cached = false;
     mgb::PathChunk work;    // reusable chunk when paths are not cached
-    mgb::DevBuf scratch_u, scratch_L, counters, origin_tot, cub_tmp;
+    mgb::DevBuf scratch_u, scratch_L, scratch_fac, counters, origin_tot, cub_tmp;
     // imager: host copies of what Image::set_coordinates_projection_surface reads (boundary points in boundary order,
     // Points::center, point2boundary[0])
     std::vector<double> h_bpos;      // [nboundary][3]

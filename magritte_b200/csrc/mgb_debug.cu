@@ -84,10 +84,13 @@ __global__ void k_ddiv(unsigned long long n, const double* a, const double* b, d
     /* ddiv2 (two numerators, one reciprocal refinement) must give ddiv's bits for both; a mismatch poisons the output */
     const unsigned long long j = (i ^ 1ull) < n ? (i ^ 1ull) : i;
     const Div2 d = ddiv2(a[i], a[j], b[i]);
-    const double w1 = ddiv(a[i], b[i]), w2 = ddiv(a[j], b[i]);
+    const double w1 = ddiv_scaled(a[i], b[i]), w2 = ddiv_scaled(a[j], b[i]);
     const bool same1 = __double_as_longlong(d.q1) == __double_as_longlong(w1) || (d.q1 != d.q1 && w1 != w1);
     const bool same2 = __double_as_longlong(d.q2) == __double_as_longlong(w2) || (d.q2 != d.q2 && w2 != w2);
     if (!(same1 && same2)) out[i] = __longlong_as_double(0x4242424242424242ll);
+    /* ddiv_raw (k_solve2's inline division on the unscaled operands) must give ddiv's bits too */
+    const double w3 = ddiv_raw(a[i], b[i]);
+    if (!(__double_as_longlong(w3) == __double_as_longlong(w1) || (w3 != w3 && w1 != w1))) out[i] = __longlong_as_double(0x4343434343434343ll);
 }
 
 // 8 independent DFMA chains per thread; explicit fma() because the file is compiled with -fmad=false.

@@ -658,35 +658,53 @@ __global__ void __launch_bounds__(32 * kSolveWarps, OFFD ? kSolveCtas / 2 : kSol
         const double S_c     = lg1 ? Sc1 : SC;
         const double avg     = 0.5 * (dt0 + dt1);
         const double invA    = avg * dt0, invC = avg * dt1;
-        const double A = 1.0 / invA, Cc = 1.0 / invC;
+        const double A = drcp(invA), Cc = drcp(invC); /* Newton reciprocal / division: the bits of 1.0 / x and a / b without nvcc's slow path */
         const double FFc = (A * F0 * FI0 + 1.0) * invC;
         const double GP  = F1 * FI1;
-        Ldiag = invC / (FFc + GP);
+        Ldiag = ddiv(invC, FFc + GP);
         u     = (S_c + A * a0 + Cc * a1) * Ldiag;
     } else if (len_f) {
         // centre == first (solver.tpp:2240-2262 with the back-substitution folded in)
         const double S_c = lg1 ? Sc1 : SC;
-        const double inv = 1.0 / dt1;
+        const double inv = drcp(dt1);
         const double Cf  = 2.0 * inv * inv;
         const double Bm  = 1.0 + 2.0 * inv;
         const double Ib  = boundary_intensity(m, o, freq);
         const double FFf = 0.5 * Bm * dt1 * dt1;
         const double GP  = F1 * FI1;
-        Ldiag = (1.0 / Cf) / (FFf + GP);
+        Ldiag = ddiv(drcp(Cf), FFf + GP);
         u     = (S_c + 2.0 * Ib * inv + Cf * a1) * Ldiag;
     } else {
         // centre == last (solver.tpp:2283-2297, 2317)
         const double S_c = lg0 ? Sn0 : SC;
-        const double inv = 1.0 / dt0;
+        const double inv = drcp(dt0);
         const double Al  = 2.0 * inv * inv;
         const double Bm  = 1.0 + 2.0 * inv;
         const double Bl  = Bm + Al;
         const double Ib  = boundary_intensity(m, o, freq);
-        Ldiag = (1.0 + F0) / (Bm + Bl * F0);
+        Ldiag = ddiv(1.0 + F0, Bm + Bl * F0);
         u     = (Al * a0 + (S_c + 2.0 * Ib * inv)) * Ldiag;
     }
 
-    // ---- Lambda increment (update_Lambda, solver.tpp:1760-1806; diagonal element only, n_off_diag = 0) ----
+    if (!OFFD) {
+        /* diagonal operator: L_diag leaves the kernel; the Lambda increment's factors (eta/chi and the line profile AT THE ORIGIN,
+           update_Lambda solver.tpp:1760-1806) depend on (o, f) only and are applied once per (o, f) by k_reduce_lambda2 instead of
+           once per (o, rr, f) here -- they were 20 % of this kernel's instructions (profiles/ncu_k_solve_r1g_c3.txt: tail + device other) */
+        if (active) { sc.u[out] = u; sc.L[out] = Ldiag; }
+        unsigned e = (active && z == 0) ? nentries : 0u;
+        unsigned g = active ? nlarge : 0u;
+#pragma unroll
+        for (int off = 16; off; off >>= 1) {
+            e += __shfl_xor_sync(0xffffffffu, e, off);
+            g += __shfl_xor_sync(0xffffffffu, g, off);
+        }
+        if (lane == 0) {
+            atomicAdd(&sc.counters[0], (unsigned long long)e);
+            if (g) atomicAdd(&sc.counters[1], (unsigned long long)g);
+        }
+        return;
+    }
+    // ---- Lambda increment (update_Lambda, solver.tpp:1760-1806) of the banded operator ----
     const double w_ang     = 2.0 * __ldg(&m.weight[rr]);
     const double freq_line = __ldg(&m.line[l]);
     const double constante = __ldg(&m.line_A[l]) * __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * w_ang;

