@@ -48,6 +48,8 @@ PYBIND11_MODULE(core, m) {
     py::class_<Image>(m, "Image")
         .def_readonly("nfreqs", &Image::nfreqs)
         .def_readonly("optical_depth", &Image::optical_depth)
+        .def_readonly("pix_begin", &Image::pix_begin)
+        .def_readonly("pix_end", &Image::pix_end)
         .def_property_readonly("ImX", [](const Image& i) { return py::array_t<double>(i.ImX.size(), i.ImX.data()); })
         .def_property_readonly("ImY", [](const Image& i) { return py::array_t<double>(i.ImY.size(), i.ImY.data()); })
         .def_property_readonly("freqs", [](const Image& i) { return py::array_t<double>(i.freqs.size(), i.freqs.data()); })
@@ -63,6 +65,13 @@ PYBIND11_MODULE(core, m) {
         .def_readonly("o_end", &Model::o_end)
         .def_static("nccl_unique_id", []() { return py::bytes(Model::nccl_unique_id()); })
         .def("set_communicator", [](Model& s, int nranks, int rank, py::bytes id) { s.set_communicator(nranks, rank, std::string(id)); })
+        .def_property_readonly("last_image_stats", [](const Model& s) {
+            py::dict d;
+            d["n_pixels"] = s.last_image_stats.n_pixels; d["n_entries"] = s.last_image_stats.n_entries; d["n_solves"] = s.last_image_stats.n_solves;
+            d["ms_trace"] = s.last_image_stats.ms_trace; d["ms_solve"] = s.last_image_stats.ms_solve; d["ms_total"] = s.last_image_stats.ms_total;
+            d["n_launches"] = s.last_image_stats.n_launches; d["max_ray_length"] = s.last_image_stats.max_ray_length;
+            return d;
+        })
         .def_property_readonly("last_stats", [](const Model& s) {
             py::dict d;
             d["n_steps"] = s.last_stats.n_steps; d["n_entries"] = s.last_stats.n_entries; d["n_solves"] = s.last_stats.n_solves;
@@ -147,6 +156,18 @@ PYBIND11_MODULE(core, m) {
         // results (copies, reference layouts)
         .def("get_J", [](const Model& s) { return out2(s.J, s.npoints, s.nfreqs); })
         .def("get_nu", [](const Model& s) { return out2(s.nu, s.npoints, s.nfreqs); })
+        .def("get_nu_rows", [](const Model& s, size_t o0, size_t o1) { /* rows [o0, o1) of radiation.frequencies.nu (a 1M-point model's nu is 7 GB) */
+            if (o1 > s.npoints || o0 > o1) throw std::runtime_error("get_nu_rows: bad range");
+            py::array_t<double> a({o1 - o0, (size_t)s.nfreqs});
+            std::copy(s.nu.begin() + o0 * s.nfreqs, s.nu.begin() + o1 * s.nfreqs, a.mutable_data());
+            return a;
+        })
+        .def("get_J_rows", [](const Model& s, size_t o0, size_t o1) {
+            if (o1 > s.npoints || o0 > o1 || s.J.size() < (size_t)s.npoints * s.nfreqs) throw std::runtime_error("get_J_rows: bad range or no J");
+            py::array_t<double> a({o1 - o0, (size_t)s.nfreqs});
+            std::copy(s.J.begin() + o0 * s.nfreqs, s.J.begin() + o1 * s.nfreqs, a.mutable_data());
+            return a;
+        })
         .def("get_emissivity", [](const Model& s) { return out2(s.emissivity, s.npoints, s.nlines()); })
         .def("get_opacity", [](const Model& s) { return out2(s.opacity, s.npoints, s.nlines()); })
         .def("get_inverse_width", [](const Model& s) { return out2(s.inverse_width, s.npoints, s.nlines()); })

@@ -419,6 +419,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
 struct Image { // reference src/model/image/image.hpp (the fields the new imager fills)
     Size nx = 0, ny = 0, nfreqs = 0;
     bool optical_depth = false; // ImageType::OpticalDepth (image.hpp) instead of Intensity
+    size_t pix_begin = 0, pix_end = 0; // the pixels this rank computed (all of them on one GPU; the other rows of I stay 0)
     double ray_direction[3] = {0, 0, 0};
     std::vector<double> ImX, ImY, I, freqs; // I [nx*ny][nfreqs]
 };
@@ -451,6 +452,7 @@ class Model {
     std::vector<Image> images;
     std::vector<double> error_mean, error_max;
     mgb_stats last_stats{};
+    mgb_image_stats last_image_stats{};
     double seconds_radiation_field = 0.0, seconds_statistical_equilibrium = 0.0; // Timer totals of model.cpp:706-724
 
     Model() = default;
@@ -895,9 +897,11 @@ class Model {
         std::vector<double> ptot((size_t)nlspecs() * npoints);
         for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
         check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+        /* one process per GPU: every pixel is independent (solver.tpp:591-622), rank r images the r-th share of the pixels */
+        im.pix_begin = npix * (size_t)rank / (size_t)nranks; im.pix_end = npix * ((size_t)rank + 1) / (size_t)nranks;
         check((optical_depth ? mgb_image_optical_depth : mgb_image_feautrier_order_2)(
-                  ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(), per_point ? 1 : 0, 0,
-                  npix, im.ImX.data(), im.ImY.data(), im.I.data(), nullptr),
+                  ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(), per_point ? 1 : 0,
+                  im.pix_begin, im.pix_end, im.ImX.data(), im.ImY.data(), im.I.data() + im.pix_begin * nfreqs, &last_image_stats),
               optical_depth ? "mgb_image_optical_depth" : "mgb_image_feautrier_order_2");
         images.push_back(std::move(im));
         return 0;

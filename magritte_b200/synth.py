@@ -70,7 +70,9 @@ def line_state(ld, pop, min_line_opacity=1.0e-13, min_line_emissivity=1.0e-50):
     return emis, opac
 
 
-def flat_from_spec(spec, params=None, min_line_opacity=1.0e-13):
+def flat_from_spec(spec, params=None, min_line_opacity=1.0e-13, with_state=True):
+    """with_state=False: geometry, thermodynamics and the static line tables only (what magritte_b200.model.build needs; the host
+    Model computes nu, the inverse widths, the LTE populations and the line state itself)."""
     position = np.ascontiguousarray(spec["position"], dtype=np.float64)
     npoints = len(position)
     direction = np.ascontiguousarray(spec["direction"], dtype=np.float64)
@@ -115,6 +117,8 @@ def flat_from_spec(spec, params=None, min_line_opacity=1.0e-13):
     if params:
         prm.update(params)
     out["params"] = prm
+    if not with_state:
+        return out
     emis, opac, invw, nu, ptot, pops = [], [], [], [], [], []
     for l, ld in enumerate(linedata):
         num = symbols.index(ld["sym"])
