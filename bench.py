@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--levelpop-iters", type=int, default=2)
     ap.add_argument("--no-config3", action="store_true", help="skip the configs[3] leg (1M points, CO + SiO-like, sparse level populations)")
     ap.add_argument("--c3-points", type=int, default=1000000)
-    ap.add_argument("--c3-pairs", type=int, default=8, help="ray pairs of the nside-8 set (384) run per radiation-field call of the configs[3] leg")
+    ap.add_argument("--c3-pairs", type=int, default=4, help="ray pairs of the nside-8 set (384) run per radiation-field call of the configs[3] leg")
     ap.add_argument("--no-config4", action="store_true", help="skip the configs[4] leg (10M-point lattice image)")
     ap.add_argument("--c4-points", type=int, default=10000000)
     ap.add_argument("--build-spec", default=None, help=argparse.SUPPRESS)  # internal: background model builder (c3 | c4)

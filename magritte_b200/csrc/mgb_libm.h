@@ -21,7 +21,7 @@
 // Proof of bit-exactness: tests/test_libm_host.py compiles this header for the host (explicit fma(),
 // -ffp-contract=off) and compares against the box's own libm over ALL 2^32 float inputs (expf, logf,
 // erff, expm1f) and a 2^32-point lattice for powf; on the GPU, mgb_selftest_libm() runs the device
-// build against host-libm results (tests/test_gpu_libm.py).
+// build against host-libm results (tests/test_gpu_parity.py::test_device_libm_bit_exact).
 //
 // The translation unit that includes this must be compiled with nvcc -fmad=false (no implicit
 // contraction); -prec-div / -prec-sqrt / no -ftz are the nvcc defaults.

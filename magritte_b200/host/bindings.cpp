@@ -1,7 +1,7 @@
 // bindings.cpp -- pybind11 module `magritte_b200.core`: the Python face of mgbh::Model, with the method names of
 // magritte.core.Model for the Feautrier order-2 path (reference src/bindings/pybindings.cpp:123-271). Arrays go in and out
-// as numpy arrays in the reference's layouts. The nested attribute tree of the reference (model.geometry.points.position.set(...))
-// is provided on the Python side by magritte_b200/model.py on top of these setters.
+// as numpy arrays in the reference's layouts through flat setters / getters; the reference's nested attribute tree
+// (model.geometry.points.position.set(...), buffer-protocol containers, Io) is the Python facade magritte_b200/core_compat.py.
 #include <pybind11/numpy.h>
 #include <pybind11/pybind11.h>
 #include <pybind11/stl.h>
@@ -140,9 +140,18 @@ PYBIND11_MODULE(core, m) {
                       [](Model& s, arr<double> d) { s.density = vec(d); })
         .def_property_readonly("column", [](const Model& s) { return s.column.empty() ? out2(s.column, 0, s.npoints) : out2(s.column, s.nrays, s.npoints); })
         // test hook: radiation.J and the diagonal Lambda lists as a radiation-field call leaves them (host-only tests of compute_Jeff / stateq)
-        .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt) {
+        .def("set_radiation_field", [](Model& s, arr<double> J, arr<double> lam, arr<uint32_t> cnt, py::object J_lines) {
             s.J = vec(J);
             const Size L = s.nlines();
+            if (!J_lines.is_none()) { /* lspec.J of the memory-sparse solver, [npoints][nlines] */
+                auto jl = J_lines.cast<arr<double>>();
+                for (Size l = 0; l < s.nlspecs(); l++) {
+                    auto& ls = s.lineProducingSpecies[l];
+                    const Size nrad = ls.linedata.nrad;
+                    for (Size p = 0; p < s.npoints; p++)
+                        for (Size k = 0; k < nrad; k++) ls.J[(size_t)p * nrad + k] = jl.data()[(size_t)p * L + s.nrad_cum[l] + k];
+                }
+            }
             for (Size l = 0; l < s.nlspecs(); l++) {
                 auto& ls = s.lineProducingSpecies[l];
                 const Size nrad = ls.linedata.nrad;
@@ -152,7 +161,7 @@ PYBIND11_MODULE(core, m) {
                         ls.lambda_cnt[(size_t)p * nrad + k] = cnt.data()[(size_t)p * L + s.nrad_cum[l] + k];
                     }
             }
-        })
+        }, py::arg("J"), py::arg("lam"), py::arg("cnt"), py::arg("J_lines") = py::none())
         // results (copies, reference layouts)
         .def("get_J", [](const Model& s) { return out2(s.J, s.npoints, s.nfreqs); })
         .def("get_nu", [](const Model& s) { return out2(s.nu, s.npoints, s.nfreqs); })
@@ -175,6 +184,31 @@ PYBIND11_MODULE(core, m) {
             const auto& ls = s.lineProducingSpecies.at(l);
             py::array_t<double> a({(size_t)s.npoints, (size_t)ls.linedata.nlev});
             for (size_t i = 0; i < ls.population.size(); i++) a.mutable_data()[i] = (double)ls.population[i];
+            return a;
+        })
+        .def("get_population_hilo", [](const Model& s, Size l) { /* the long double populations as hi + lo doubles */
+            const auto& ls = s.lineProducingSpecies.at(l);
+            py::array_t<double> hi({(size_t)s.npoints, (size_t)ls.linedata.nlev}), lo({(size_t)s.npoints, (size_t)ls.linedata.nlev});
+            for (size_t i = 0; i < ls.population.size(); i++) {
+                hi.mutable_data()[i] = (double)ls.population[i];
+                lo.mutable_data()[i] = (double)(ls.population[i] - (LD)hi.data()[i]);
+            }
+            return py::make_tuple(hi, lo);
+        })
+        .def("set_population", [](Model& s, Size l, arr<double> hi, arr<double> lo, arr<double> tot) { /* checkpoint / resume (lineProducingSpecies.cpp:49-71) */
+            auto& ls = s.lineProducingSpecies.at(l);
+            if ((size_t)hi.size() != ls.population.size() || (size_t)lo.size() != ls.population.size() || (size_t)tot.size() != ls.population_tot.size())
+                throw std::runtime_error("set_population: wrong size");
+            for (size_t i = 0; i < ls.population.size(); i++) ls.population[i] = (LD)hi.data()[i] + (LD)lo.data()[i];
+            std::copy(tot.data(), tot.data() + tot.size(), ls.population_tot.begin());
+            ls.populations.clear(); ls.residuals.clear();
+            ls.populations.push_back(ls.population);
+        })
+        .def("refresh_line_state_from_populations", [](Model& s) { s.set_emissivity_and_opacity(); })
+        .def("get_lambda_cnt", [](const Model& s, Size l) {
+            const auto& ls = s.lineProducingSpecies.at(l);
+            py::array_t<uint32_t> a({(size_t)s.npoints, (size_t)ls.linedata.nrad});
+            std::copy(ls.lambda_cnt.begin(), ls.lambda_cnt.end(), a.mutable_data());
             return a;
         })
         .def("get_population_tot", [](const Model& s, Size l) { const auto& v = s.lineProducingSpecies.at(l).population_tot; return py::array_t<double>(v.size(), v.data()); })
