@@ -91,6 +91,11 @@ int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* position, con
                      uint32_t nrays, const double* direction, const double* weight, const uint32_t* antipod,
                      uint32_t nboundary, const uint32_t* point2boundary, const int32_t* boundary_condition,
                      const double* boundary_temperature, int spherical_symmetry);
+/* Rays::use_adaptive_directions (rays.hpp:23-31, rays.cpp:37-100): one ray set PER POINT, direction [npoints][nrays][3] and weight
+ * [npoints][nrays] (what Rays::read finds when the direction array has nrays*npoints rows). Call after mgb_set_geometry, whose
+ * direction / weight arguments then hold point 0's set (the antipode table is derived from it for all points, like the reference).
+ * Selects the <..., true> instantiations of Geometry::get_next / get_shift and Rays::get_weight (model.cpp:357-389). */
+int mgb_set_adaptive_directions(mgb_ctx* ctx, const double* direction, const double* weight);
 /* thermodynamics.temperature.gas, thermodynamics.turbulence.vturb2 (both [npoints]). */
 int mgb_set_thermodynamics(mgb_ctx* ctx, const double* temperature_gas, const double* vturb2);
 /* Static line tables (Lines::read, src/model/lines/lines.cpp:11-69): per species nrad and

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("MGB_LIB") or os.path.join(_HERE, "lib", "libmagritte_b200.so")  # MGB_LIB: A/B builds of the same library
 
 EXPORTS = [
-    "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_thermodynamics",
+    "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_adaptive_directions", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
     "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
@@ -140,8 +140,9 @@ class Context:
         vel, pvel = _p(f["velocity"], np.float64)
         nn, pnn = _p(f["n_neighbors"], np.uint32)
         nb, pnb = _p(f["neighbors"], np.uint32)
-        d, pd = _p(f["direction"], np.float64)
-        w, pw = _p(f["weight"], np.float64)
+        adaptive = bool(f.get("use_adaptive_directions", False))  # direction / weight then hold one ray set per point
+        d, pd = _p(np.asarray(f["direction"]).reshape(-1, 3)[:self.nrays], np.float64)
+        w, pw = _p(np.asarray(f["weight"]).reshape(-1)[:self.nrays], np.float64)
         ap, pap = _p(f["antipod"], np.uint32)
         p2b, pp2b = _p(f["point2boundary"], np.uint32)
         bc, pbc = _p(f["boundary_condition"], np.int32)
@@ -150,6 +151,11 @@ class Context:
                                               C.c_uint64(int(nn.sum(dtype=np.uint64))), C.c_uint32(self.nrays), pd, pw, pap,
                                               C.c_uint32(int(f["nboundary"])), pp2b, pbc, pbt,
                                               C.c_int(int(f["spherical_symmetry"]))), "mgb_set_geometry")
+        if adaptive:
+            da, pda = _p(f["direction"], np.float64)
+            wa, pwa = _p(f["weight"], np.float64)
+            assert da.size == 3 * self.npoints * self.nrays and wa.size == self.npoints * self.nrays
+            self._check(self.lib.mgb_set_adaptive_directions(self._ctx, pda, pwa), "mgb_set_adaptive_directions")
         T, pT = _p(f["temperature"], np.float64)
         vt, pvt = _p(f["vturb2"], np.float64)
         self._check(self.lib.mgb_set_thermodynamics(self._ctx, pT, pvt), "mgb_set_thermodynamics")

@@ -521,10 +521,15 @@ class Model:
         cum[1:] = np.cumsum(nn[:-1], dtype=np.uint64)
         g.points.cum_n_neighbors.set(cum.astype(np.uint32))  # Points::read (points.cpp:44-60)
         d = np.asarray(io.read_array("geometry/rays/direction"), dtype=np.float64).reshape(-1, 3)
-        g.rays.use_adaptive_directions = str(io.read_attr(".adaptive_ray_tracing", "false")) == "true"
+        nrays = P.nrays()
+        if len(d) == nrays:  # Rays::read decides from the length of the direction array (rays.cpp:10-19)
+            g.rays.use_adaptive_directions = False
+        elif len(d) == nrays * npoints:
+            g.rays.use_adaptive_directions = True
+        else:
+            P.set_nrays(len(d))  # raises like the reference: "will error, and give some more info on the sizes of the arrays"
         g.rays.direction.set(d)
         g.rays.weight.set(np.asarray(io.read_array("geometry/rays/weight"), dtype=np.float64).reshape(-1))
-        nrays = P.nrays()
         P.set_hnrays(nrays // 2)
         from .synth import antipodes
         g.rays.antipod.set(antipodes(d[:nrays]))  # Rays::read (rays.cpp:52-63)
@@ -609,8 +614,6 @@ class Model:
                 p2b[b2p] = np.arange(len(b2p), dtype=np.uint32)
                 self.geometry.boundary.point2boundary._assign(p2b)
                 self.lines.line = np.array([f for ls in self.lines.lineProducingSpecies for f in ls.linedata.frequency], dtype=np.float64)
-            if self.geometry.rays.use_adaptive_directions:
-                raise RuntimeError("magritte_b200: adaptive ray directions are not supported by this build")
             old = self._core
             self._core = hostmodel.from_reference(self, self.device)
             if self._comm is not None:

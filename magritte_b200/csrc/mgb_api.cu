@@ -157,6 +157,7 @@ extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* po
     }
     DevModel& m = ctx->m;
     m.npoints = npoints; m.nrays = nrays; m.hnrays = nrays / 2; m.nboundary = nboundary; m.spherical = spherical_symmetry ? 1 : 0;
+    m.adaptive = 0;
     m.pos = ctx->pos.as<double4>(); m.vel = ctx->vel.as<double4>(); m.csr = ctx->csr.as<uint2>(); m.nbs = ctx->nbs.as<uint32_t>();
     m.dir = ctx->dir.as<double>(); m.weight = ctx->weight.as<double>(); m.antipod = ctx->antipod.as<uint32_t>();
     m.p2b = ctx->p2b.as<uint32_t>(); m.bcond = ctx->bcond.as<int32_t>(); m.btemp = ctx->btemp.as<double>();
@@ -165,6 +166,25 @@ extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* po
     ctx->lens_o0 = ctx->lens_o1 = 0;
     ctx->drop_chunks();
     ctx->points_dirty = true;
+    ctx->res_valid = false;
+    return MGB_OK;
+}
+
+// Rays::use_adaptive_directions (rays.hpp:23-31): a ray set per point. direction [npoints][nrays][3], weight [npoints][nrays]; the antipode
+// table stays the one of mgb_set_geometry (the reference derives it from point 0's set and assumes it for every point, rays.cpp:52-63).
+extern "C" int mgb_set_adaptive_directions(mgb_ctx* ctx, const double* direction, const double* weight) {
+    if (!ctx) return MGB_EINVAL;
+    if (!ctx->have_geometry) return ctx->fail(MGB_ESTATE, "mgb_set_adaptive_directions before mgb_set_geometry");
+    if (!direction || !weight) return ctx->fail(MGB_EINVAL, "mgb_set_adaptive_directions: null argument");
+    cudaSetDevice(ctx->device);
+    const size_t n = (size_t)ctx->m.npoints * ctx->m.nrays;
+    MGB_TRY(upload(ctx, ctx->dir, direction, sizeof(double) * 3 * n));
+    MGB_TRY(upload(ctx, ctx->weight, weight, sizeof(double) * n));
+    MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->m.dir = ctx->dir.as<double>(); ctx->m.weight = ctx->weight.as<double>();
+    ctx->m.adaptive = 1;
+    ctx->lens_o0 = ctx->lens_o1 = 0; /* every path changes */
+    ctx->drop_chunks();
     ctx->res_valid = false;
     return MGB_OK;
 }

@@ -705,7 +705,7 @@ __global__ void __launch_bounds__(32 * kSolveWarps, OFFD ? kSolveCtas / 2 : kSol
         return;
     }
     // ---- Lambda increment (update_Lambda, solver.tpp:1760-1806) of the banded operator ----
-    const double w_ang     = 2.0 * __ldg(&m.weight[rr]);
+    const double w_ang     = 2.0 * ray_weight(m, o, rr); /* get_weight<adaptive>(nr[centre], rr), solver.tpp:1777 */
     const double freq_line = __ldg(&m.line[l]);
     const double constante = __ldg(&m.line_A[l]) * __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * w_ang;
     double eta_l, chi_l;
@@ -831,7 +831,7 @@ __global__ void k_reduce_J(DevModel m, uint32_t o0, uint32_t no, const double* _
     double acc = 0.0;
     for (uint32_t rr = 0; rr < m.hnrays; rr++) {
         const double v = u[((size_t)rr * no + ol) * m.nfreqs + f];
-        acc += v * 2.0 * __ldg(&m.weight[rr]);
+        acc += v * 2.0 * ray_weight(m, o0 + ol, rr);
         if (u_full) u_full[((size_t)rr * u_no + (o0 + ol - u_o0)) * m.nfreqs + f] = v;
     }
     J[(size_t)(o0 + ol) * m.nfreqs + f] = acc;
@@ -846,7 +846,7 @@ __global__ void k_reduce_J_lines(DevModel m, uint32_t o0, uint32_t no, const dou
     const uint32_t ol = (uint32_t)(i / m.nlines), l = (uint32_t)(i % m.nlines);
     double acc = 0.0;
     for (uint32_t rr = 0; rr < m.hnrays; rr++) {
-        const double wt = __ldg(&m.weight[rr]) * 2.0;
+        const double wt = ray_weight(m, o0 + ol, rr) * 2.0;
         for (uint32_t z = 0; z < m.nquads; z++)
             acc += __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * wt * u[((size_t)rr * no + ol) * m.nfreqs + (size_t)l * m.nquads + z];
     }

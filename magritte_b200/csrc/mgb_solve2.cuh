@@ -571,7 +571,7 @@ __global__ void __launch_bounds__(128) k_reduce_lambda2(const __grid_constant__ 
     for (uint32_t rr = 0; rr < m.hnrays; rr++) {
         const uint32_t ar = __ldg(&m.antipod[rr]);
         if (lens[(size_t)o * m.nrays + rr] + lens[(size_t)o * m.nrays + ar] == 0) continue; /* n_tot <= 1: no add_element */
-        const double w_ang = 2.0 * __ldg(&m.weight[rr]);
+        const double w_ang = 2.0 * ray_weight(m, o, rr);
         for (uint32_t z = 0; z < m.nquads; z++) {
             const uint32_t f = l * m.nquads + z;
             const double constante = A_l * __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * w_ang;

@@ -92,6 +92,11 @@ PYBIND11_MODULE(core, m) {
             s.set_geometry((Size)nn.size(), pos.data(), vel.data(), nn.data(), nbs.data(), (size_t)nbs.size(), (Size)w.size(), dir.data(), w.data(),
                            anti.data(), (Size)b2p.size(), b2p.data(), bc.data(), bt.data());
         })
+        .def("set_adaptive_directions", [](Model& s, arr<double> dir, arr<double> w) {
+            if ((size_t)w.size() != (size_t)s.npoints * s.nrays || (size_t)dir.size() != 3 * (size_t)s.npoints * s.nrays)
+                throw std::runtime_error("set_adaptive_directions: direction must be [npoints * nrays][3], weight [npoints * nrays]");
+            s.set_adaptive_directions(dir.data(), w.data());
+        })
         .def("set_thermodynamics", [](Model& s, arr<double> T, arr<double> v) { s.set_thermodynamics(T.data(), v.data()); })
         .def("set_abundance", [](Model& s, arr<double> ab) { s.set_abundance(ab.data(), (Size)ab.shape(1)); })
         .def("add_species", [](Model& s, py::dict d) {

@@ -489,7 +489,7 @@ class Model {
     void set_geometry(Size np, const double* pos, const double* vel, const Size* n_nbs, const Size* nbs, size_t n_nbs_tot, Size nr,
                       const double* dir, const double* wgt, const Size* anti, Size nb, const Size* b2p, const int32_t* bcond,
                       const double* btemp) {
-        npoints = np; nrays = nr; nboundary = nb;
+        npoints = np; nrays = nr; nboundary = nb; use_adaptive_directions = false;
         position.assign(pos, pos + 3 * (size_t)np); velocity.assign(vel, vel + 3 * (size_t)np);
         n_neighbors.assign(n_nbs, n_nbs + np); neighbors.assign(nbs, nbs + n_nbs_tot);
         direction.assign(dir, dir + 3 * (size_t)nr); weight.assign(wgt, wgt + nr); antipod.assign(anti, anti + nr);
@@ -498,6 +498,19 @@ class Model {
         for (Size b = 0; b < nb; b++) point2boundary[b2p[b]] = b;
         boundary_condition.assign(bcond, bcond + nb); boundary_temperature.assign(btemp, btemp + nb);
         dirty_geometry = true;
+    }
+    // Rays::use_adaptive_directions (rays.hpp:23-31): dir [npoints][nrays][3], wgt [npoints][nrays]; after set_geometry (point 0's set)
+    std::vector<double> direction_adaptive, weight_adaptive;
+    bool use_adaptive_directions = false;
+    void set_adaptive_directions(const double* dir, const double* wgt) {
+        direction_adaptive.assign(dir, dir + 3 * (size_t)npoints * nrays); weight_adaptive.assign(wgt, wgt + (size_t)npoints * nrays);
+        use_adaptive_directions = true; dirty_geometry = true;
+    }
+    void upload_geometry() {
+        check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
+                               direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
+                               boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
+        if (use_adaptive_directions) check(mgb_set_adaptive_directions(ctx, direction_adaptive.data(), weight_adaptive.data()), "mgb_set_adaptive_directions");
     }
     void set_thermodynamics(const double* T, const double* vt2) {
         temperature_gas.assign(T, T + npoints); vturb2.assign(vt2, vt2 + npoints);
@@ -869,9 +882,7 @@ class Model {
             if (rc != MGB_OK) { ctx = nullptr; throw std::runtime_error(std::string("mgb_create failed: ") + mgb_last_error(nullptr)); }
         }
         if (dirty_geometry) {
-            check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
-                                   direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
-                                   boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
+            upload_geometry();
             dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true;
         }
         column.resize((size_t)nrays * npoints);
@@ -1013,9 +1024,7 @@ class Model {
         prm.n_off_diag = parameters.n_off_diag; prm.store_intensities = 0;
         check(mgb_set_params(ctx, &prm), "mgb_set_params");
         if (dirty_geometry) {
-            check(mgb_set_geometry(ctx, npoints, position.data(), velocity.data(), n_neighbors.data(), neighbors.data(), neighbors.size(), nrays,
-                                   direction.data(), weight.data(), antipod.data(), nboundary, point2boundary.data(), boundary_condition.data(),
-                                   boundary_temperature.data(), parameters.spherical_symmetry ? 1 : 0), "mgb_set_geometry");
+            upload_geometry();
             dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true; have_partition = false;
         }
         if (dirty_thermo) { check(mgb_set_thermodynamics(ctx, temperature_gas.data(), vturb2.data()), "mgb_set_thermodynamics"); dirty_thermo = false; }

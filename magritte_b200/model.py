@@ -58,8 +58,12 @@ def build(flat, species, abundance, parameters, device=0):
     P = m.mutable_parameters()
     for k, v in parameters.items():
         setattr(P, k, v)
-    m.set_geometry(flat["position"], flat["velocity"], flat["n_neighbors"], flat["neighbors"], flat["direction"], flat["weight"],
+    nrays = int(flat["nrays"])
+    d, w = np.asarray(flat["direction"], dtype=np.float64).reshape(-1, 3), np.asarray(flat["weight"], dtype=np.float64).reshape(-1)
+    m.set_geometry(flat["position"], flat["velocity"], flat["n_neighbors"], flat["neighbors"], np.ascontiguousarray(d[:nrays]), np.ascontiguousarray(w[:nrays]),
                    flat["antipod"], flat["boundary2point"], flat["boundary_condition"], flat["boundary_temperature"])
+    if flat.get("use_adaptive_directions"):  # one ray set per point (Rays::use_adaptive_directions)
+        m.set_adaptive_directions(d, w)
     m.set_thermodynamics(flat["temperature"], flat["vturb2"])
     m.set_abundance(np.ascontiguousarray(abundance, dtype=np.float64))
     for s in species:

@@ -214,7 +214,7 @@ def load_species(name):
 # --------------------------------------------------------------------------------------
 def assemble(core, io, name, *, dimension, spherical, position, velocity, nbs, n_nbs, boundary2point,
              direction, weight, symbols, abundance, temperature, vturb2, linedata, nquads,
-             boundary_condition="CMB", boundary_temperature=None):
+             boundary_condition="CMB", boundary_temperature=None, use_adaptive_directions=False):
     """Build a model through the pybind setters, write it to `io`, read it back (required:
     reference Lines::read builds the derived line tables, src/model/lines/lines.cpp:11-69) and
     return the freshly read model."""
@@ -225,7 +225,7 @@ def assemble(core, io, name, *, dimension, spherical, position, velocity, nbs, n
     P.set_model_name(name)
     P.set_dimension(int(dimension))
     P.set_npoints(int(npoints))
-    P.set_nrays(int(len(direction)))
+    P.set_nrays(int(len(direction)) // (npoints if use_adaptive_directions else 1))  # adaptive: direction is [npoints * nrays][3]
     P.set_nspecs(len(symbols))
     P.set_nlspecs(len(linedata))
     P.set_nquads(int(nquads))
@@ -247,7 +247,7 @@ def assemble(core, io, name, *, dimension, spherical, position, velocity, nbs, n
     m.geometry.boundary.boundary_temperature.set(np.ascontiguousarray(boundary_temperature, dtype=np.float64))
     m.geometry.rays.direction.set(np.ascontiguousarray(direction, dtype=np.float64))
     m.geometry.rays.weight.set(np.ascontiguousarray(weight, dtype=np.float64))
-    m.geometry.rays.use_adaptive_directions = False
+    m.geometry.rays.use_adaptive_directions = bool(use_adaptive_directions)
     m.lines.resize_LineProducingSpecies(len(linedata))
     roots, weights = gauss_hermite(nquads)
     for l, ld in enumerate(linedata):
@@ -384,6 +384,30 @@ def spec_wind_3d(npoints=100000, nside_rays=4, nquads=11, nside_shell=None, seed
                 boundary2point=boundary2point, direction=direction, weight=weight, symbols=symbols,
                 abundance=abundance, temperature=temperature, vturb2=vturb2, linedata=linedata,
                 nquads=nquads)
+
+
+def with_adaptive_directions(spec, seed=99):
+    """The same model with Rays::use_adaptive_directions (rays.hpp:23-31): every point gets its own rotation of the ray set (antipodal
+    pairs stay pairs, as the reference assumes, rays.cpp:52-63) and its own weights (pair-symmetric, normalised per point)."""
+    rng = np.random.default_rng(seed)
+    out = dict(spec)
+    d, w = np.asarray(spec["direction"], dtype=np.float64), np.asarray(spec["weight"], dtype=np.float64)
+    N, R = len(spec["position"]), len(d)
+    dirs, wts = np.empty((N, R, 3)), np.empty((N, R))
+    h = R // 2
+    for p in range(N):
+        q, _ = np.linalg.qr(rng.normal(size=(3, 3)))
+        dd = d @ q.T
+        dd /= np.linalg.norm(dd, axis=1)[:, None]
+        dd[h:] = -dd[:h]  # exact antipodes, as in the HEALPix-based sets
+        f = rng.uniform(0.5, 1.5, h)
+        ww = np.concatenate([w[:h] * f, w[h:] * f])
+        dirs[p], wts[p] = dd, ww / ww.sum()
+    if spec.get("spherical") or int(spec.get("dimension", 3)) == 1:
+        raise ValueError("adaptive directions: 3D models only")
+    out["direction"], out["weight"] = dirs.reshape(N * R, 3), wts.reshape(N * R)
+    out["use_adaptive_directions"] = True
+    return out
 
 
 def build(core, io, name, spec):

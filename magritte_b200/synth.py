@@ -76,7 +76,8 @@ def flat_from_spec(spec, params=None, min_line_opacity=1.0e-13, with_state=True)
     position = np.ascontiguousarray(spec["position"], dtype=np.float64)
     npoints = len(position)
     direction = np.ascontiguousarray(spec["direction"], dtype=np.float64)
-    nrays = len(direction)
+    adaptive = bool(spec.get("use_adaptive_directions", False))
+    nrays = len(direction) // (npoints if adaptive else 1)  # adaptive: [npoints * nrays][3] (rays.cpp:13-19)
     b2p = np.asarray(spec["boundary2point"], dtype=np.uint32)
     p2b = np.full(npoints, npoints, dtype=np.uint32)
     p2b[b2p] = np.arange(len(b2p), dtype=np.uint32)
@@ -100,8 +101,8 @@ def flat_from_spec(spec, params=None, min_line_opacity=1.0e-13, with_state=True)
                position=position, velocity=np.ascontiguousarray(spec["velocity"], dtype=np.float64),
                n_neighbors=n_nbs, neighbors=np.ascontiguousarray(spec["nbs"], dtype=np.uint32),
                cum_n_neighbors=cum.astype(np.uint32), direction=direction,
-               weight=np.ascontiguousarray(spec["weight"], dtype=np.float64), antipod=antipodes(direction),
-               use_adaptive_directions=False, boundary2point=b2p, point2boundary=p2b,
+               weight=np.ascontiguousarray(spec["weight"], dtype=np.float64), antipod=antipodes(direction[:nrays]),
+               use_adaptive_directions=adaptive, boundary2point=b2p, point2boundary=p2b,
                boundary_condition=np.full(len(b2p), {"Zero": 0, "Thermal": 1, "CMB": 2}[bc_name], dtype=np.int32),
                boundary_temperature=np.full(len(b2p), 2.72548) if bt is None else np.asarray(bt, dtype=np.float64),
                temperature=T, vturb2=vt2, nrad=nrad,

@@ -41,7 +41,8 @@ class OrcModel(C.Structure):
         ("max_interpolation_diff", C.c_double), ("max_width_fraction", C.c_double),
         ("J", _f64p), ("u", _f64p), ("L_val", _f64p), ("L_nr", _u32p), ("L_cnt", _u32p),
         ("criterion", _f64p), ("dshift_max", _f64p),
-        ("stat_steps", C.c_uint64), ("stat_nbs", C.c_uint64), ("stat_entries", C.c_uint64), ("max_length", C.c_uint32)]
+        ("stat_steps", C.c_uint64), ("stat_nbs", C.c_uint64), ("stat_entries", C.c_uint64), ("max_length", C.c_uint32),
+        ("adaptive_directions", C.c_int32)]
 
 
 def _ptr(a, t):
@@ -76,6 +77,7 @@ class Oracle:
             assert f[k].flags["C_CONTIGUOUS"], k
             setattr(m, k, _ptr(f[k], t))
         m.max_inverse_mass = f["max_inverse_mass"]
+        m.adaptive_directions = 1 if f.get("use_adaptive_directions") else 0
         for k in ("min_opacity", "max_distance_opacity_contribution", "max_interpolation_diff", "max_width_fraction"):
             setattr(m, k, float(prm[k]))
         N, F, L = m.npoints, m.nfreqs, m.nlines
