@@ -384,6 +384,7 @@ int ensure_lens(mgb_ctx* ctx, uint32_t o0, uint32_t o1, mgb_stats* st, uint32_t&
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
     const uint32_t no = o1 - o0;
     const size_t nw   = (size_t)no * m.nrays;
+    NvtxRange nvtx("mgb: ray lengths (k_trace count pass)");
     EventTimer t(ctx->stream);
     t.start();
     PathView pv{};
@@ -418,6 +419,7 @@ int fill_chunk(mgb_ctx* ctx, PathChunk& ch, mgb_stats* st, uint32_t& launches) {
     MGB_CUDA(ctx, ch.nr.ensure(4 * (size_t)ch.steps));
     MGB_CUDA(ctx, ch.dZ.ensure(8 * (size_t)ch.steps));
     MGB_CUDA(ctx, ch.shift.ensure(8 * (size_t)ch.steps));
+    NvtxRange nvtx("mgb: ray paths (k_trace fill pass)");
     EventTimer t(ctx->stream);
     t.start();
     const uint32_t* lens_chunk = ctx->lens.as<uint32_t>() + (size_t)ch.o0 * m.nrays;
@@ -563,6 +565,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         return MGB_OK;
     }
     uint32_t launches = 0;
+    NvtxRange nvtx_run("mgb_run_feautrier_order_2");
     EventTimer total(ctx->stream);
     total.start();
     MGB_TRY(refresh_points(ctx));
@@ -646,12 +649,16 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         pv.nr = ch->nr.as<uint32_t>(); pv.dZ = ch->dZ.as<double>(); pv.shift = ch->shift.as<double>(); pv.shift0 = ch->shift0.as<double>();
         ScratchView sc{ctx->scratch_u.as<double>(), ctx->scratch_L.as<double>(), ctx->counters.as<unsigned long long>(),
                        ctx->scratch_offV.as<double>(), ctx->scratch_offN.as<uint32_t>(), K};
+        {
+        NvtxRange nvtx_solve("mgb: k_solve (eta/chi + Feautrier sweep)");
         EventTimer ts(ctx->stream);
         ts.start();
         if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f));
         else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_solve<APPROX_ONELINE>(ctx, pv, sc, nchunks_f));
         else MGB_CUDA(ctx, launch_solve<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f));
         st.ms_solve += ts.stop();
+        }
+        NvtxRange nvtx_reduce("mgb: J / Lambda reduction");
         st.n_solve_launches++;
         launches++;
         EventTimer tr(ctx->stream);

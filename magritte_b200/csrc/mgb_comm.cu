@@ -129,6 +129,7 @@ extern "C" int mgb_allgather_results(mgb_ctx* ctx) {
     if ((int)ctx->part_bounds.size() != ctx->nranks + 1)
         return ctx->fail(MGB_ESTATE, "mgb_allgather_results: call mgb_partition or mgb_partition_balanced with nranks = %d first", ctx->nranks);
     ncclComm_t comm = (ncclComm_t)ctx->comm;
+    mgb::NvtxRange nvtx("mgb_allgather_results (NCCL)");
     // all-gather with per-rank row counts, in place: every rank's slice already sits at its global rows, one broadcast per owner
     ncclResult_t r = g_nccl.GroupStart();
     char* J = (char*)ctx->J.p; char* lv = (char*)ctx->lam_val.p; char* lc = (char*)ctx->lam_cnt.p; char* jl = (char*)ctx->J_lines.p;

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h> /* header-only NVTX 3: ranges show up in nsys / ncu timelines, no-ops without a tool attached */
 
 #include "../../include/magritte_b200.h"
 #include "mgb_device.cuh"
@@ -63,6 +64,14 @@ struct LpSpecies { // LineProducingSpecies + Linedata (lineProducingSpecies.hpp,
         for (auto* b : populations) delete b;
         for (auto* b : residuals) delete b;
     }
+};
+
+// NVTX range for the lifetime of the object (one per phase of a call: trace, solve, reduce, all-gather, statistical equilibrium ...)
+struct NvtxRange {
+    explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+    ~NvtxRange() { nvtxRangePop(); }
+    NvtxRange(const NvtxRange&) = delete;
+    NvtxRange& operator=(const NvtxRange&) = delete;
 };
 
 } // namespace mgb

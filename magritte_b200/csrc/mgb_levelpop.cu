@@ -669,6 +669,7 @@ extern "C" int mgb_lp_get_line_state(mgb_ctx* ctx, double* emissivity, double* o
 extern "C" int mgb_lp_compute_Jeff(mgb_ctx* ctx, int sparse) {
     if (!ctx) return MGB_EINVAL;
     MGB_TRY(all_species_ready(ctx, "mgb_lp_compute_Jeff"));
+    NvtxRange nvtx("mgb_lp_compute_Jeff");
     if (!ctx->res_valid || ctx->res_o0 != 0 || ctx->res_o1 != ctx->m.npoints)
         return ctx->fail(MGB_ESTATE, "mgb_lp_compute_Jeff: the radiation field is not complete on this device (rows [%u,%u) of %u; run all origins or "
                                      "mgb_allgather_results first)", ctx->res_o0, ctx->res_o1, ctx->m.npoints);
@@ -717,6 +718,7 @@ static int finish_update(mgb_ctx* ctx, double pop_prec, mgb_lp_convergence* conv
 extern "C" int mgb_lp_update_statistical_equilibrium(mgb_ctx* ctx, int keep_history, double pop_prec, mgb_lp_convergence* conv, float* ms) {
     if (!ctx) return MGB_EINVAL;
     MGB_TRY(all_species_ready(ctx, "mgb_lp_update_statistical_equilibrium"));
+    NvtxRange nvtx("mgb_lp_update_statistical_equilibrium");
     if (!ctx->have_state) return ctx->fail(MGB_ESTATE, "mgb_lp_update_statistical_equilibrium: no line state");
     cudaSetDevice(ctx->device);
     cudaEvent_t ea = nullptr, eb = nullptr;
