@@ -53,7 +53,11 @@ PYBIND11_MODULE(core, m) {
         .def_property_readonly("ImX", [](const Image& i) { return py::array_t<double>(i.ImX.size(), i.ImX.data()); })
         .def_property_readonly("ImY", [](const Image& i) { return py::array_t<double>(i.ImY.size(), i.ImY.data()); })
         .def_property_readonly("freqs", [](const Image& i) { return py::array_t<double>(i.freqs.size(), i.freqs.data()); })
-        .def_property_readonly("I", [](const Image& i) { return out2(i.I, (size_t)i.nx * i.ny, i.nfreqs); });
+        .def_property_readonly("I", [](const Image& i) {
+            py::array_t<double> a({(size_t)i.nx * i.ny, (size_t)i.nfreqs});
+            std::copy(i.I.data(), i.I.data() + i.I.size(), a.mutable_data());
+            return a;
+        });
 
     py::class_<Model>(m, "Model")
         .def(py::init<>())

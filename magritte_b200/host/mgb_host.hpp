@@ -21,6 +21,7 @@
 #include <cstdint>
 #include <ctime>
 #include <limits>
+#include <memory>
 #include <numeric>
 #include <stdexcept>
 #include <string>
@@ -421,7 +422,17 @@ struct Image { // reference src/model/image/image.hpp (the fields the new imager
     bool optical_depth = false; // ImageType::OpticalDepth (image.hpp) instead of Intensity
     size_t pix_begin = 0, pix_end = 0; // the pixels this rank computed (all of them on one GPU; the other rows of I stay 0)
     double ray_direction[3] = {0, 0, 0};
-    std::vector<double> ImX, ImY, I, freqs; // I [nx*ny][nfreqs]
+    std::vector<double> ImX, ImY, freqs;
+    // Image.I [nx*ny][nfreqs]: 210 MB for 512^2 x 100 -- allocated WITHOUT the zero fill of std::vector (the device writes every row of this
+    // rank's pixel range; only the rows outside it are cleared)
+    struct Pixels {
+        std::unique_ptr<double[]> p;
+        size_t n = 0;
+        void allocate(size_t count) { p.reset(new double[count]); n = count; }
+        double* data() { return p.get(); }
+        const double* data() const { return p.get(); }
+        size_t size() const { return n; }
+    } I;
 };
 
 enum SpectralDiscretisation { SD_None, SD_Lines, SD_Image }; // model.hpp
@@ -541,6 +552,7 @@ class Model {
     // ---- Lines::set_inverse_width (lines.tpp:45-59) ----
     int compute_inverse_line_widths() {
         const Size L = nlines();
+        state_serial++;
         for (Size p = 0; p < npoints; p++)
             for (Size l = 0; l < nlspecs(); l++)
                 for (Size k = 0; k < lineProducingSpecies[l].linedata.nrad; k++) {
@@ -553,6 +565,7 @@ class Model {
     // ---- Lines::set_emissivity_and_opacity (lines.tpp:29-41) ----
     void set_emissivity_and_opacity() {
         const Size L = nlines();
+        state_serial++;
 #pragma omp parallel for schedule(static)
         for (Size p = 0; p < npoints; p++)
             for (Size l = 0; l < nlspecs(); l++)
@@ -883,7 +896,7 @@ class Model {
         }
         if (dirty_geometry) {
             upload_geometry();
-            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true;
+            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true; state_uploaded = 0;
         }
         column.resize((size_t)nrays * npoints);
         check(mgb_set_column(ctx, density.data(), 0, npoints, column.data(), nullptr), "mgb_set_column");
@@ -901,19 +914,24 @@ class Model {
         const double n = 1 / std::sqrt(rx * rx + ry * ry + rz * rz);
         im.ray_direction[0] = rx * n; im.ray_direction[1] = ry * n; im.ray_direction[2] = rz * n;
         const size_t npix = (size_t)Nxpix * Nypix;
-        im.ImX.resize(npix); im.ImY.resize(npix); im.I.resize(npix * nfreqs);
+        im.ImX.resize(npix); im.ImY.resize(npix); im.I.allocate(npix * nfreqs);
         const double dir[3] = {rx, ry, rz};
         const bool per_point = spectralDiscretisation == SD_Lines;
         im.freqs = per_point ? std::vector<double>() : image_nu;
         std::vector<double> ptot((size_t)nlspecs() * npoints);
         for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
-        check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+        if (state_uploaded != state_serial) { /* the imager reads the line state: upload it only when the host arrays changed since the last upload */
+            check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
+            state_uploaded = state_serial;
+        }
         /* one process per GPU: every pixel is independent (solver.tpp:591-622), rank r images the r-th share of the pixels */
         im.pix_begin = npix * (size_t)rank / (size_t)nranks; im.pix_end = npix * ((size_t)rank + 1) / (size_t)nranks;
         check((optical_depth ? mgb_image_optical_depth : mgb_image_feautrier_order_2)(
                   ctx, approx(), (int)parameters.dimension, dir, Nxpix, Nypix, nfreqs, per_point ? nu.data() : image_nu.data(), per_point ? 1 : 0,
                   im.pix_begin, im.pix_end, im.ImX.data(), im.ImY.data(), im.I.data() + im.pix_begin * nfreqs, &last_image_stats),
               optical_depth ? "mgb_image_optical_depth" : "mgb_image_feautrier_order_2");
+        if (im.pix_begin) std::fill(im.I.data(), im.I.data() + im.pix_begin * nfreqs, 0.0);
+        if (im.pix_end < npix) std::fill(im.I.data() + im.pix_end * nfreqs, im.I.data() + npix * nfreqs, 0.0);
         images.push_back(std::move(im));
         return 0;
     }
@@ -923,6 +941,7 @@ class Model {
     bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true, dirty_species = true, comm_dirty = false;
     std::string comm_id;
     bool have_partition = false;
+    unsigned long state_serial = 1, state_uploaded = 0; // host emissivity / opacity / inverse_width changed <-> last upload for the imager
     // One radiation-field pass on this rank's origins (+ the all-gather): Solver::solve_feautrier_order_2[_sparse] (solver.tpp:297-363, 458-540).
     // upload_state: the host's emissivity / opacity / inverse_width go up first (the host-twin path); otherwise the device table is current.
     void run_radiation_field(const bool upload_state) {
@@ -991,6 +1010,7 @@ class Model {
             check(mgb_lp_get_Jeff(ctx, l, ls.Jlin.data(), ls.Jeff.data()), "mgb_lp_get_Jeff");
         }
         check(mgb_lp_get_line_state(ctx, emissivity.data(), opacity.data(), nullptr), "mgb_lp_get_line_state");
+        state_serial++;
         std::vector<double> jl((size_t)npoints * L), lam((size_t)npoints * L);
         std::vector<uint32_t> cnt((size_t)npoints * L);
         if (!sparse) { J.resize((size_t)npoints * nfreqs); check(mgb_get_J(ctx, 0, npoints, J.data()), "mgb_get_J"); }
@@ -1025,7 +1045,7 @@ class Model {
         check(mgb_set_params(ctx, &prm), "mgb_set_params");
         if (dirty_geometry) {
             upload_geometry();
-            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true; have_partition = false;
+            dirty_geometry = false; dirty_thermo = dirty_lines = dirty_freqs = true; have_partition = false; state_uploaded = 0;
         }
         if (dirty_thermo) { check(mgb_set_thermodynamics(ctx, temperature_gas.data(), vturb2.data()), "mgb_set_thermodynamics"); dirty_thermo = false; }
         if (dirty_lines) {
@@ -1036,7 +1056,7 @@ class Model {
                 qw.insert(qw.end(), l.quadrature_weights.begin(), l.quadrature_weights.end());
             }
             check(mgb_set_lines(ctx, nlspecs(), nrad.data(), im.data(), line.data(), A.data(), nquads(), qw.data()), "mgb_set_lines");
-            dirty_lines = false; dirty_freqs = true; dirty_species = true;
+            dirty_lines = false; dirty_freqs = true; dirty_species = true; state_uploaded = 0;
         }
         if (comm_dirty) {
             check(mgb_comm_init(ctx, nranks, rank, comm_id.data()), "mgb_comm_init");
