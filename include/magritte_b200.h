@@ -50,7 +50,7 @@ typedef struct mgb_params {
     uint64_t path_cache_bytes;                /* HBM budget for cached ray paths; 0 = library default */
     uint64_t scratch_bytes;                   /* HBM budget for per-chunk u/Lambda scratch; 0 = default */
     uint32_t cache_paths;                     /* 1: keep traced paths across calls when they fit the budget */
-    uint32_t reserved;
+    uint32_t anisotropic;                     /* 1: also accumulate the anisotropic radiation-field tensor (mgb_get_J_anis) */
 } mgb_params;
 
 /* Work and timing counters of the last mgb_run_feautrier_order_2 (Sigma S, Sigma D, Sigma N). */
@@ -133,6 +133,11 @@ int mgb_get_lambda(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* lambd
  * accumulates it next to J from the same solves, in the reference's rr > line > z order. */
 int mgb_get_J_lines(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* J_lines);
 int mgb_get_u(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* u);
+/* Solver::solve_feautrier_order_2_anis (solver.tpp:365-456; Model::compute_radiation_field_feautrier_order_2_anis, model.cpp:435-470): the
+ * same solves accumulated per line into lspec.J and the five anisotropic tensor elements J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im
+ * (lineProducingSpecies.hpp:29-35) with du = w_z * weight(o,rr) * u, J += 2 du, J2_x += wt_x(n) * du in the reference's rr > line > z
+ * order. Needs params.anisotropic = 1 for the run. out [6][(o_end-o_begin)][nlines] in that order of quantities. */
+int mgb_get_J_anis(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* out);
 /* n_off_diag = K > 0 (banded approximate Lambda operator, Solver::update_Lambda solver.tpp:1806-1850 with L_lower/L_upper of
  * :2320-2355): the (p, line) lists of Lambda::add_element (lambda.tpp:79-89) in the reference's insertion order.
  * capacity = 1 + 2*K*hnrays entries per list; list_val / list_nr [(o_end-o_begin)][nlines][capacity] (unused tail: 0 / 0xffffffff),

@@ -21,7 +21,7 @@ EXPORTS = [
     "mgb_allgather_results", "mgb_comm_destroy", "mgb_comm_agree", "mgb_set_radiation_field", "mgb_lp_set_parameters", "mgb_lp_set_species", "mgb_lp_add_collision_partner", "mgb_lp_set_abundance",
     "mgb_lp_set_populations", "mgb_lp_get_populations", "mgb_lp_refresh_line_state", "mgb_lp_get_line_state", "mgb_lp_compute_Jeff", "mgb_lp_get_Jeff",
     "mgb_lp_update_statistical_equilibrium", "mgb_lp_ng_gram", "mgb_lp_ng_combine", "mgb_lp_finish_update", "mgb_lp_trial_convergence",
-    "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_image_optical_depth", "mgb_set_column",
+    "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_get_J_anis", "mgb_image_optical_depth", "mgb_set_column",
 ]
 
 
@@ -30,7 +30,7 @@ class Params(C.Structure):
                 ("max_interpolation_diff", C.c_double), ("max_width_fraction", C.c_double),
                 ("n_off_diag", C.c_uint32), ("store_intensities", C.c_uint32),
                 ("path_cache_bytes", C.c_uint64), ("scratch_bytes", C.c_uint64),
-                ("cache_paths", C.c_uint32), ("reserved", C.c_uint32)]
+                ("cache_paths", C.c_uint32), ("anisotropic", C.c_uint32)]
 
 
 class Stats(C.Structure):
@@ -239,6 +239,13 @@ class Context:
         J = np.empty((o1 - o0, self.nlines))
         self._check(self.lib.mgb_get_J_lines(self._ctx, C.c_uint32(o0), C.c_uint32(o1), J.ctypes.data_as(C.c_void_p)), "mgb_get_J_lines")
         return J
+
+    def get_J_anis(self, o_range=None):
+        """(J, J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im) per line, each [rows][nlines] (run with set_params(anisotropic=1))."""
+        o0, o1 = o_range or self.last_range
+        out = np.empty((6, o1 - o0, self.nlines))
+        self._check(self.lib.mgb_get_J_anis(self._ctx, C.c_uint32(o0), C.c_uint32(o1), out.ctypes.data_as(C.c_void_p)), "mgb_get_J_anis")
+        return out
 
     def get_lambda(self, o_range=None):
         o0, o1 = o_range or self.last_range

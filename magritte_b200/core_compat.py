@@ -709,6 +709,13 @@ class Model:
         self._pull_radiation(sparse=True)
         return 0
 
+    def compute_radiation_field_feautrier_order_2_anis(self):
+        c = self._sync()
+        c.compute_radiation_field_feautrier_order_2_anis()
+        for l, ls in enumerate(self.lines.lineProducingSpecies):
+            ls.J, ls.J2_0, ls.J2_1_Re, ls.J2_1_Im, ls.J2_2_Re, ls.J2_2_Im = c.get_J_anis(l)
+        return 0
+
     def compute_Jeff(self):
         c = self._sync()
         c.compute_Jeff()
@@ -778,5 +785,5 @@ class Model:
     def _not_on_path(self, *a, **k):
         raise RuntimeError("this solver is outside the Feautrier order-2 path magritte_b200 implements")
     compute_radiation_field_shortchar_order_0 = compute_radiation_field_feautrier_order_2_uv = _not_on_path
-    compute_radiation_field_feautrier_order_2_anis = compute_level_populations_shortchar = compute_image = _not_on_path
+    compute_level_populations_shortchar = compute_image = _not_on_path
     compute_image_optical_depth = compute_image_for_point = set_eta_and_chi = set_boundary_condition = _not_on_path

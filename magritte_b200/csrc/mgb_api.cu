@@ -46,6 +46,7 @@ extern "C" int mgb_params_default(mgb_params* p) {
     p->path_cache_bytes                  = 48ull << 30;
     p->scratch_bytes                     = 8ull << 30;
     p->cache_paths                       = 1;
+    p->anisotropic                       = 0;
     return MGB_OK;
 }
 
@@ -615,6 +616,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         MGB_CUDA(ctx, ctx->u_full.ensure(8 * (size_t)m.hnrays * (o_end - o_begin) * m.nfreqs));
         u_full = ctx->u_full.as<double>(); ctx->u_o0 = o_begin; ctx->u_no = o_end - o_begin;
     }
+    if (ctx->params.anisotropic) MGB_CUDA(ctx, ctx->J_anis.ensure(8 * 6 * prow * m.nlines));
     uint32_t max_no = 0;
     for (auto* c : ctx->chunks) max_no = std::max(max_no, c->o1 - c->o0);
     MGB_CUDA(ctx, ctx->scratch_u.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
@@ -666,6 +668,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         const size_t nj = (size_t)no * m.nfreqs, nl = (size_t)no * m.nlines;
         k_reduce_J<<<(unsigned)((nj + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J.as<double>(), u_full, ctx->u_o0, ctx->u_no);
         k_reduce_J_lines<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_lines.as<double>());
+        if (ctx->params.anisotropic) { k_reduce_anis<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_anis.as<double>()); launches++; }
         if (K)
             k_reduce_lambda_banded<<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(
                 m, ch->o0, no, K, ctx->lam_cap, ctx->lens.as<uint32_t>(), sc.L, sc.offV, sc.offN, ctx->lam_list_val.as<double>(),
@@ -694,7 +697,7 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     st.n_chunks = (uint32_t)ctx->chunks.size();
     st.n_launches = launches;
     st.paths_cached = all_cached ? 1 : 0;
-    ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true;
+    ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true; ctx->res_anis = ctx->params.anisotropic != 0;
     if (stats) *stats = st;
     return MGB_OK;
 }
@@ -721,6 +724,19 @@ extern "C" int mgb_get_J_lines(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, d
     cudaSetDevice(ctx->device);
     const size_t L = ctx->m.nlines;
     MGB_CUDA(ctx, cudaMemcpy(J_lines, ctx->J_lines.as<double>() + (size_t)o_begin * L, 8 * (size_t)(o_end - o_begin) * L, cudaMemcpyDeviceToHost));
+    return MGB_OK;
+}
+
+extern "C" int mgb_get_J_anis(mgb_ctx* ctx, uint32_t o_begin, uint32_t o_end, double* out) {
+    if (!ctx || !out) return MGB_EINVAL;
+    MGB_TRY(check_range(ctx, o_begin, o_end, "mgb_get_J_anis"));
+    if (!ctx->res_anis || !ctx->J_anis.p) return ctx->fail(MGB_ESTATE, "mgb_get_J_anis: the last run did not have params.anisotropic set");
+    if (ctx->nranks > 1 && (int)ctx->part_bounds.size() == ctx->nranks + 1 && (o_begin < ctx->part_bounds[ctx->rank] || o_end > ctx->part_bounds[ctx->rank + 1]))
+        return ctx->fail(MGB_EUNSUPPORTED, "mgb_get_J_anis: the anisotropic tensor is not part of the all-gather; ask for this rank's own rows");
+    cudaSetDevice(ctx->device);
+    const size_t L = ctx->m.nlines, plane = (size_t)ctx->m.npoints * L, rows = (size_t)(o_end - o_begin) * L;
+    for (int q = 0; q < 6; q++)
+        MGB_CUDA(ctx, cudaMemcpy(out + q * rows, ctx->J_anis.as<double>() + q * plane + (size_t)o_begin * L, 8 * rows, cudaMemcpyDeviceToHost));
     return MGB_OK;
 }
 

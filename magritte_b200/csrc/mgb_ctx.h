@@ -99,7 +99,8 @@ struct mgb_ctx {
     mgb::DevBuf nu, corr_line;
     mgb::DevBuf stage_a, stage_b, stage_c, stage_d; // H2D staging of the per-iteration line state
     // results
-    mgb::DevBuf J, J_lines, lam_val, lam_cnt, u_full;
+    mgb::DevBuf J, J_lines, J_anis, lam_val, lam_cnt, u_full;
+    bool res_anis = false;           // the last run filled J_anis
     mgb::DevBuf lam_list_val, lam_list_nr, scratch_offV, scratch_offN; // banded Lambda operator (n_off_diag > 0)
     uint32_t lam_cap = 1;
     uint32_t u_o0 = 0, u_no = 0;

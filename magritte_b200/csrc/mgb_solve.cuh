@@ -853,6 +853,34 @@ __global__ void k_reduce_J_lines(DevModel m, uint32_t o0, uint32_t no, const dou
     J_lines[(size_t)(o0 + ol) * m.nlines + l] = acc;
 }
 
+// Solver::solve_feautrier_order_2_anis (solver.tpp:365-456): per (o, line) the isotropic J and the five elements of the anisotropic
+// radiation-field tensor, du = w_z * weight(o, rr) * u, J += 2 du, J2_x += wt_x(n(o, rr)) * du, loop nest rr > line > z.
+// out [6][npoints][nlines]: J, J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im.
+__global__ void k_reduce_anis(DevModel m, uint32_t o0, uint32_t no, const double* __restrict__ u, double* __restrict__ out) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (size_t)no * m.nlines) return;
+    const uint32_t ol = (uint32_t)(i / m.nlines), l = (uint32_t)(i % m.nlines);
+    const uint32_t o  = o0 + ol;
+    const double sqrt3 = sqrt(3.0), inv_sqrt2 = 1.0 / sqrt(2.0); /* tools/types.hpp:46-48 */
+    double J = 0.0, J20 = 0.0, J21r = 0.0, J21i = 0.0, J22r = 0.0, J22i = 0.0;
+    for (uint32_t rr = 0; rr < m.hnrays; rr++) {
+        const size_t ri  = ray_index(m, o, rr);
+        const double wt  = __ldg(&m.weight[ri]);
+        const double nx = __ldg(&m.dir[3 * ri]), ny = __ldg(&m.dir[3 * ri + 1]), nz = __ldg(&m.dir[3 * ri + 2]);
+        const double wt_0    = inv_sqrt2 * (3.0 * nz * nz - 1.0);
+        const double wt_1_Re = -sqrt3 * nx * nz;
+        const double wt_1_Im = -sqrt3 * ny * nz;
+        const double wt_2_Re = 0.5 * sqrt3 * (nx * nx - ny * ny);
+        const double wt_2_Im = sqrt3 * nx * ny;
+        for (uint32_t z = 0; z < m.nquads; z++) {
+            const double du = __ldg(&m.line_quadw[(size_t)l * m.nquads + z]) * wt * u[((size_t)rr * no + ol) * m.nfreqs + (size_t)l * m.nquads + z];
+            J += 2.0 * du; J20 += wt_0 * du; J21r += wt_1_Re * du; J21i += wt_1_Im * du; J22r += wt_2_Re * du; J22i += wt_2_Im * du;
+        }
+    }
+    const size_t plane = (size_t)m.npoints * m.nlines, at = (size_t)o * m.nlines + l;
+    out[at] = J; out[plane + at] = J20; out[2 * plane + at] = J21r; out[3 * plane + at] = J21i; out[4 * plane + at] = J22r; out[5 * plane + at] = J22i;
+}
+
 // Lambda(o, lid) = sum over rr, then z, of the increments, in the order Lambda::add_element saw them
 // (solver.tpp:476-508 loop nest rr > k > z; lambda.tpp:79-89).
 __global__ void k_reduce_lambda(DevModel m, uint32_t o0, uint32_t no, const uint32_t* __restrict__ lens, const double* __restrict__ L,

@@ -140,6 +140,12 @@ PYBIND11_MODULE(core, m) {
         .def("compute_level_populations", &Model::compute_level_populations)
         .def("compute_radiation_field_feautrier_order_2_sparse", &Model::compute_radiation_field_feautrier_order_2_sparse)
         .def("compute_Jeff_sparse", &Model::compute_Jeff_sparse)
+        .def("compute_radiation_field_feautrier_order_2_anis", &Model::compute_radiation_field_feautrier_order_2_anis)
+        .def("get_J_anis", [](const Model& s, Size l) { /* (J, J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im) of species l, each [npoints][nrad] */
+            const auto& ls = s.lineProducingSpecies.at(l);
+            return py::make_tuple(out2(ls.J, s.npoints, ls.linedata.nrad), out2(ls.J2_0, s.npoints, ls.linedata.nrad), out2(ls.J2_1_Re, s.npoints, ls.linedata.nrad),
+                                  out2(ls.J2_1_Im, s.npoints, ls.linedata.nrad), out2(ls.J2_2_Re, s.npoints, ls.linedata.nrad), out2(ls.J2_2_Im, s.npoints, ls.linedata.nrad));
+        })
         .def("compute_level_populations_from_stateq_sparse", &Model::compute_level_populations_from_stateq_sparse)
         .def("compute_level_populations_sparse", &Model::compute_level_populations_sparse)
         .def("compute_image_new", &Model::compute_image_new)

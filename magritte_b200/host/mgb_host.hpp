@@ -192,6 +192,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
     std::vector<VecLD> populations, residuals;
     std::vector<Real> Jlin, Jeff, Jdif;      // [npoints][nrad]
     std::vector<Real> J;                     // [npoints][nrad] line-integrated mean intensity of the memory-sparse solver (lspec.J)
+    std::vector<Real> J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im; // [npoints][nrad] anisotropic radiation-field tensor (lineProducingSpecies.hpp:29-35)
     std::vector<Real> lambda_Ls;             // [npoints][nrad] the diagonal ALO element (nr == p), lambda.tpp:79-89
     std::vector<Size> lambda_cnt;            // [npoints][nrad] list length (0 or 1)
     Real fraction_not_converged = 0, relative_change_mean = 0, relative_change_max = 0;
@@ -688,6 +689,29 @@ class Model {
         }
         return 0;
     }
+    // ---- Model::compute_radiation_field_feautrier_order_2_anis (model.cpp:435-470; Solver::solve_feautrier_order_2_anis, solver.tpp:365-456):
+    //      the same solves accumulated into lspec.J and the anisotropic tensor elements lspec.J2_0 .. J2_2_Im ----
+    int compute_radiation_field_feautrier_order_2_anis() {
+        if (nranks > 1) throw std::runtime_error("compute_radiation_field_feautrier_order_2_anis: one GPU only (the tensor is not part of the all-gather)");
+        anisotropic = true;
+        try { run_radiation_field(true); } catch (...) { anisotropic = false; throw; }
+        anisotropic = false;
+        const Size L = nlines();
+        std::vector<double> a((size_t)6 * npoints * L);
+        check(mgb_get_J_anis(ctx, 0, npoints, a.data()), "mgb_get_J_anis");
+        const size_t plane = (size_t)npoints * L;
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& ls = lineProducingSpecies[l];
+            const Size nrad = ls.linedata.nrad;
+            std::vector<Real>* dst[6] = {&ls.J, &ls.J2_0, &ls.J2_1_Re, &ls.J2_1_Im, &ls.J2_2_Re, &ls.J2_2_Im};
+            for (int q = 0; q < 6; q++) {
+                dst[q]->assign((size_t)npoints * nrad, 0.0);
+                for (Size p = 0; p < npoints; p++)
+                    for (Size k = 0; k < nrad; k++) (*dst[q])[(size_t)p * nrad + k] = a[q * plane + (size_t)p * L + nrad_cum[l] + k];
+            }
+        }
+        return 0;
+    }
     // ---- Model::compute_Jeff_sparse (model.cpp:549-570) ----
     int compute_Jeff_sparse() {
         for (Size l = 0; l < nlspecs(); l++) {
@@ -954,7 +978,7 @@ class Model {
     mgb_ctx* ctx = nullptr;
     bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true, dirty_species = true, comm_dirty = false;
     std::string comm_id;
-    bool have_partition = false;
+    bool have_partition = false, anisotropic = false;
     unsigned long state_serial = 1, state_uploaded = 0; // host emissivity / opacity / inverse_width changed <-> last upload for the imager
     // One radiation-field pass on this rank's origins (+ the all-gather): Solver::solve_feautrier_order_2[_sparse] (solver.tpp:297-363, 458-540).
     // upload_state: the host's emissivity / opacity / inverse_width go up first (the host-twin path); otherwise the device table is current.
@@ -1055,7 +1079,7 @@ class Model {
         mgb_params_default(&prm);
         prm.min_opacity = parameters.min_opacity; prm.max_distance_opacity_contribution = parameters.max_distance_opacity_contribution;
         prm.max_interpolation_diff = parameters.max_interpolation_diff; prm.max_width_fraction = parameters.max_width_fraction;
-        prm.n_off_diag = parameters.n_off_diag; prm.store_intensities = 0;
+        prm.n_off_diag = parameters.n_off_diag; prm.store_intensities = 0; prm.anisotropic = anisotropic ? 1 : 0;
         check(mgb_set_params(ctx, &prm), "mgb_set_params");
         if (dirty_geometry) {
             upload_geometry();

@@ -114,6 +114,29 @@ class Oracle:
         return dict(nr=nr[:k], nr_interp=nri[:k], interp_factor=fac[:k], shift=sh[:k], dZ=dz[:max(k - 1, 0)],
                     centre_offset=coff.value, n_tot=k)
 
+    def anis(self):
+        """Solver::solve_feautrier_order_2_anis (solver.tpp:365-456) from the stored u of a solve(): (J, J2_0, J2_1_Re, J2_1_Im, J2_2_Re,
+        J2_2_Im), each [npoints][nlines], accumulated in the reference's order (rr outside z, one rounding per operation)."""
+        f, m = self.flat, self.m
+        assert self.u is not None, "Oracle(store_u=True) and solve() first"
+        N, H, L, nq, R = m.npoints, m.hnrays, m.nlines, m.nquads, m.nrays
+        d = np.asarray(f["direction"], dtype=np.float64).reshape(-1, 3)
+        w = np.asarray(f["weight"], dtype=np.float64).reshape(-1)
+        qw = np.repeat(np.asarray(f["quad_weights"]), np.asarray(f["nrad"]), axis=0)  # [nlines][nquads]
+        sqrt3, inv_sqrt2 = np.sqrt(3.0), 1.0 / np.sqrt(2.0)
+        out = np.zeros((6, N, L))
+        pts = np.arange(N)
+        for rr in range(H):
+            idx = pts * R + rr if m.adaptive_directions else np.full(N, rr)
+            nx, ny, nz, wt = d[idx, 0], d[idx, 1], d[idx, 2], w[idx]
+            wts = (None, inv_sqrt2 * (3.0 * nz * nz - 1.0), -sqrt3 * nx * nz, -sqrt3 * ny * nz, 0.5 * sqrt3 * (nx * nx - ny * ny), sqrt3 * nx * ny)
+            for z in range(nq):
+                du = qw[None, :, z] * wt[:, None] * self.u[rr].reshape(N, L, nq)[:, :, z]
+                out[0] += 2.0 * du
+                for q in range(1, 6):
+                    out[q] += wts[q][:, None] * du
+        return out
+
     def solve(self, o_range=None, rr_range=None, half_length=None, twosided=False):
         """twosided=False: the reference's elimination order (the oracle). twosided=True: the product's two-sided
         re-ordering of the same solve, restated operation for operation (bit-comparable with the CUDA kernel)."""
