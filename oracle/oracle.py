@@ -42,7 +42,7 @@ class OrcModel(C.Structure):
         ("J", _f64p), ("u", _f64p), ("L_val", _f64p), ("L_nr", _u32p), ("L_cnt", _u32p),
         ("criterion", _f64p), ("dshift_max", _f64p),
         ("stat_steps", C.c_uint64), ("stat_nbs", C.c_uint64), ("stat_entries", C.c_uint64), ("max_length", C.c_uint32),
-        ("adaptive_directions", C.c_int32)]
+        ("adaptive_directions", C.c_int32), ("min_dtau", C.c_double)]
 
 
 def _ptr(a, t):
@@ -80,6 +80,7 @@ class Oracle:
         m.adaptive_directions = 1 if f.get("use_adaptive_directions") else 0
         for k in ("min_opacity", "max_distance_opacity_contribution", "max_interpolation_diff", "max_width_fraction"):
             setattr(m, k, float(prm[k]))
+        m.min_dtau = float(prm.get("min_dtau", 1.0e-15))
         N, F, L = m.npoints, m.nfreqs, m.nlines
         self.J = np.zeros((N, F))
         self.u = np.zeros((m.hnrays, N, F)) if store_u else None
@@ -148,6 +149,19 @@ class Oracle:
         if self.threads:
             os.environ["OMP_NUM_THREADS"] = str(self.threads)
         rc = self.lib.orc_solve(C.byref(m), C.c_uint32(o0), C.c_uint32(o1), C.c_uint32(r0), C.c_uint32(r1), C.c_uint32(hl))
+        assert rc == 0
+        return self.J
+
+    def shortchar(self, o_range=None, rr_range=None, half_length=None):
+        """Solver::solve_shortchar_order_0 (solver.tpp:150-235): J, u = (I_f + I_b) / 2 and the local Lambda elements (two adds per
+        (origin, ray pair, frequency), one per half ray) in the reference's order."""
+        m = self.m
+        o0, o1 = o_range or (0, m.npoints)
+        r0, r1 = rr_range or (0, m.hnrays)
+        hl = half_length or self.max_length()
+        if self.threads:
+            os.environ["OMP_NUM_THREADS"] = str(self.threads)
+        rc = self.lib.orc_shortchar(C.byref(m), C.c_uint32(o0), C.c_uint32(o1), C.c_uint32(r0), C.c_uint32(r1), C.c_uint32(hl))
         assert rc == 0
         return self.J
 
