@@ -121,6 +121,13 @@ int mgb_set_params(mgb_ctx* ctx, const mgb_params* p);
  * o in [o_begin, o_end) and all hnrays ray pairs: trace, eta/chi, Feautrier order-2 solve, J and Lambda
  * accumulation, results left in device memory. Synchronous. `stats` may be NULL. */
 int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats);
+/* Solver::setup + Solver::solve_shortchar_order_0<approx>(Model&) (solver.tpp:150-235; the half-ray integrations
+ * solve_shortchar_order_0_ray_forward / _backward, :1564-1654 / :1664-1757; Model::compute_radiation_field_shortchar_order_0,
+ * model.cpp:313-349): same traced paths, chunks and result arrays as the Feautrier run -- J, u = (I_f + I_b) / 2 (with
+ * store_intensities), and the LOCAL Lambda element only (n_off_diag is ignored, like the reference does). min_dtau is
+ * Parameters::min_dtau (1e-15). A half ray without a segment contributes the factor 0 to its Lambda element (the
+ * reference reads an uninitialised dtau there). */
+int mgb_run_shortchar_order_0(mgb_ctx* ctx, int approx, double min_dtau, uint32_t o_begin, uint32_t o_end, mgb_stats* stats);
 /* Copy results of the last run to the host. J: rows [o_begin,o_end) of radiation.J, (o_end-o_begin)*nfreqs.
  * Lambda (n_off_diag = 0: the diagonal operator): lambda_val [(o_end-o_begin)][nlines] holds Ls for the
  * element (p=o, k, nr=o) that Lambda::add_element accumulated (lambda.tpp:79-89), lambda_cnt the list

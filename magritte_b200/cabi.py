@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("MGB_LIB") or os.path.join(_HERE, "lib", "libmagritte_
 EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_adaptive_directions", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
-    "mgb_run_feautrier_order_2", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
+    "mgb_run_feautrier_order_2", "mgb_run_shortchar_order_0", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
     "mgb_allgather_results", "mgb_comm_destroy", "mgb_comm_agree", "mgb_set_radiation_field", "mgb_lp_set_parameters", "mgb_lp_set_species", "mgb_lp_add_collision_partner", "mgb_lp_set_abundance",
     "mgb_lp_set_populations", "mgb_lp_get_populations", "mgb_lp_refresh_line_state", "mgb_lp_get_line_state", "mgb_lp_compute_Jeff", "mgb_lp_get_Jeff",
@@ -212,6 +212,17 @@ class Context:
         st = Stats()
         self._check(self.lib.mgb_run_feautrier_order_2(self._ctx, C.c_int(approx), C.c_uint32(o0), C.c_uint32(o1),
                                                        C.byref(st)), "mgb_run_feautrier_order_2")
+        self.last_range = (o0, o1)
+        return st
+
+    def run_shortchar(self, approx=2, o_range=None, min_dtau=1.0e-15, store_u=None):
+        """Solver::solve_shortchar_order_0 (solver.tpp:150-235) -> Stats; results through get_J / get_u / get_lambda_diag."""
+        o0, o1 = o_range or (0, self.npoints)
+        if store_u is not None:
+            self.set_params(store_intensities=1 if store_u else 0)
+        st = Stats()
+        self._check(self.lib.mgb_run_shortchar_order_0(self._ctx, C.c_int(approx), C.c_double(min_dtau), C.c_uint32(o0), C.c_uint32(o1),
+                                                       C.byref(st)), "mgb_run_shortchar_order_0")
         self.last_range = (o0, o1)
         return st
 

@@ -716,6 +716,12 @@ class Model:
             ls.J, ls.J2_0, ls.J2_1_Re, ls.J2_1_Im, ls.J2_2_Re, ls.J2_2_Im = c.get_J_anis(l)
         return 0
 
+    def compute_radiation_field_shortchar_order_0(self):
+        c = self._sync()
+        c.compute_radiation_field_shortchar_order_0()
+        self._pull_radiation()
+        return 0
+
     def compute_Jeff(self):
         c = self._sync()
         c.compute_Jeff()
@@ -747,6 +753,14 @@ class Model:
         n = c.compute_level_populations_sparse(bool(use_Ng_acceleration), int(max_niterations))
         self._pull_lines()
         self._pull_radiation(sparse=True)
+        self.error_mean, self.error_max = list(c.error_mean), list(c.error_max)
+        return n
+
+    def compute_level_populations_shortchar(self, use_Ng_acceleration, max_niterations):
+        c = self._sync()
+        n = c.compute_level_populations_shortchar(bool(use_Ng_acceleration), int(max_niterations))
+        self._pull_lines()
+        self._pull_radiation()
         self.error_mean, self.error_max = list(c.error_mean), list(c.error_max)
         return n
 
@@ -784,6 +798,5 @@ class Model:
     # the reference binds these too; they are other solvers (SURVEY.md 2.1 "non-target solvers")
     def _not_on_path(self, *a, **k):
         raise RuntimeError("this solver is outside the Feautrier order-2 path magritte_b200 implements")
-    compute_radiation_field_shortchar_order_0 = compute_radiation_field_feautrier_order_2_uv = _not_on_path
-    compute_level_populations_shortchar = compute_image = _not_on_path
+    compute_radiation_field_feautrier_order_2_uv = compute_image = _not_on_path
     compute_image_optical_depth = compute_image_for_point = set_eta_and_chi = set_boundary_condition = _not_on_path

@@ -8,6 +8,7 @@
 
 #include "mgb_ctx.h"
 #include "mgb_solve2.cuh"
+#include "mgb_shortchar.cuh"
 
 using namespace mgb;
 
@@ -471,6 +472,17 @@ cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc
     return ctx->solve_v2 ? launch_solve_v2<APPROX>(ctx, pv, sc) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
 }
 template <int APPROX>
+cudaError_t launch_shortchar(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f, double min_dtau) {
+    const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
+    const size_t blocks = (nitems + kSolveWarps - 1) / kSolveWarps;
+    const size_t smem   = kSolveWarps * solve_smem_per_warp(ctx->lines_per_warp);
+    cudaError_t e = cudaFuncSetAttribute(k_shortchar<APPROX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_shortchar<APPROX><<<(unsigned)blocks, 32 * kSolveWarps, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
+                                                                                ctx->lines_per_warp, min_dtau);
+    return cudaGetLastError();
+}
+template <int APPROX>
 cudaError_t launch_reduce_lambda2(mgb_ctx* ctx, uint32_t o0, uint32_t no, const ScratchView& sc) {
     const size_t nl = (size_t)no * ctx->m.nlines;
     k_reduce_lambda2<APPROX><<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(ctx->m, o0, no, ctx->lens.as<uint32_t>(), sc.L, ctx->lam_val.as<double>(),
@@ -547,11 +559,15 @@ extern "C" int mgb_timer_stop(mgb_ctx* ctx, float* ms) {
     return MGB_OK;
 }
 
-extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats) {
+// The radiation-field run of both solvers: `shortchar` = false is Solver::solve_feautrier_order_2 (solver.tpp:458-540), true is
+// Solver::solve_shortchar_order_0 (solver.tpp:150-235) on the same traced paths, origin chunks and J / Lambda result arrays.
+static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats, bool shortchar, double min_dtau) {
+    const char* who = shortchar ? "mgb_run_shortchar_order_0" : "mgb_run_feautrier_order_2";
     if (!ctx) return MGB_EINVAL;
     if (!(ctx->have_geometry && ctx->have_thermo && ctx->have_lines && ctx->have_freqs && ctx->have_state))
-        return ctx->fail(MGB_ESTATE, "mgb_run_feautrier_order_2: model incomplete (geometry %d thermo %d lines %d freqs %d state %d)",
+        return ctx->fail(MGB_ESTATE, "%s: model incomplete (geometry %d thermo %d lines %d freqs %d state %d)", who,
                          ctx->have_geometry, ctx->have_thermo, ctx->have_lines, ctx->have_freqs, ctx->have_state);
+    if (shortchar && !(min_dtau > 0.0)) return ctx->fail(MGB_EINVAL, "%s: min_dtau must be positive (Parameters::min_dtau = 1e-15)", who);
     if (approx < 0 || approx > 2) return ctx->fail(MGB_EINVAL, "approx must be 0 (None), 1 (OneLine) or 2 (CloseLines)");
     DevModel& m = ctx->m;
     if (o_begin > o_end || o_end > m.npoints) return ctx->fail(MGB_EINVAL, "origin range [%u,%u) invalid for npoints = %u", o_begin, o_end, m.npoints);
@@ -561,12 +577,12 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     if (o_begin == o_end) { /* a rank that owns no origin (nranks > npoints, or a very skewed cost partition): a successful no-op that still
                                owns result buffers, so that the peers' collective in mgb_allgather_results does not hang on it */
         MGB_TRY(mgb_internal_alloc_results(ctx));
-        ctx->res_o0 = ctx->res_o1 = o_begin; ctx->res_K = ctx->params.n_off_diag; ctx->res_valid = true;
+        ctx->res_o0 = ctx->res_o1 = o_begin; ctx->res_K = shortchar ? 0 : ctx->params.n_off_diag; ctx->res_valid = true;
         if (stats) *stats = st;
         return MGB_OK;
     }
     uint32_t launches = 0;
-    NvtxRange nvtx_run("mgb_run_feautrier_order_2");
+    NvtxRange nvtx_run(who);
     EventTimer total(ctx->stream);
     total.start();
     MGB_TRY(refresh_points(ctx));
@@ -574,8 +590,8 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
 
     const uint32_t nchunks_f = ctx->n_freq_chunks;
     // ---- plan origin chunks: bounded scratch (16 B per solve) and bounded path bytes (20 B per step) ----
-    const uint32_t K = ctx->params.n_off_diag;
-    const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * (16 + 24 * (size_t)K);
+    const uint32_t K = shortchar ? 0 : ctx->params.n_off_diag; /* the short-characteristics solver only has the local Lambda element */
+    const size_t per_origin_scratch = (size_t)m.hnrays * m.nfreqs * (shortchar ? 24 : 16 + 24 * (size_t)K);
     const uint32_t max_o_scratch    = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / per_origin_scratch);
     unsigned long long range_steps  = 0;
     for (uint32_t o = o_begin; o < o_end; o++) range_steps += ctx->origin_steps[o - ctx->lens_o0];
@@ -616,7 +632,8 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         MGB_CUDA(ctx, ctx->u_full.ensure(8 * (size_t)m.hnrays * (o_end - o_begin) * m.nfreqs));
         u_full = ctx->u_full.as<double>(); ctx->u_o0 = o_begin; ctx->u_no = o_end - o_begin;
     }
-    if (ctx->params.anisotropic) MGB_CUDA(ctx, ctx->J_anis.ensure(8 * 6 * prow * m.nlines));
+    const bool anis = ctx->params.anisotropic && !shortchar;
+    if (anis) MGB_CUDA(ctx, ctx->J_anis.ensure(8 * 6 * prow * m.nlines));
     uint32_t max_no = 0;
     for (auto* c : ctx->chunks) max_no = std::max(max_no, c->o1 - c->o0);
     MGB_CUDA(ctx, ctx->scratch_u.ensure(8 * (size_t)m.hnrays * max_no * m.nfreqs));
@@ -627,7 +644,8 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         const char* v2 = getenv("MGB_SOLVE_V2");
         ctx->solve_v2 = v2 && v2[0] == '1';
     }
-    const bool lambda2 = !K; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
+    const bool lambda2 = !K && !shortchar; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
+    if (shortchar) MGB_CUDA(ctx, ctx->scratch_offV.ensure(16 * (size_t)m.hnrays * max_no * m.nfreqs)); /* the two half-ray factors of each (rr, o, f) */
     if (lambda2) MGB_CUDA(ctx, ctx->scratch_fac.ensure(16 * (size_t)max_no * m.nfreqs));
     if (K) { /* banded operator: at most 1 + 2K distinct points per ray pair (lambda.tpp:79-89 lists) */
         ctx->lam_cap = 1 + 2 * K * m.hnrays;
@@ -655,7 +673,11 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         NvtxRange nvtx_solve("mgb: k_solve (eta/chi + Feautrier sweep)");
         EventTimer ts(ctx->stream);
         ts.start();
-        if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f));
+        if (shortchar) {
+            if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_shortchar<APPROX_NONE>(ctx, pv, sc, nchunks_f, min_dtau));
+            else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_shortchar<APPROX_ONELINE>(ctx, pv, sc, nchunks_f, min_dtau));
+            else MGB_CUDA(ctx, launch_shortchar<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f, min_dtau));
+        } else if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_solve<APPROX_NONE>(ctx, pv, sc, nchunks_f));
         else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_solve<APPROX_ONELINE>(ctx, pv, sc, nchunks_f));
         else MGB_CUDA(ctx, launch_solve<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f));
         st.ms_solve += ts.stop();
@@ -668,8 +690,13 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
         const size_t nj = (size_t)no * m.nfreqs, nl = (size_t)no * m.nlines;
         k_reduce_J<<<(unsigned)((nj + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J.as<double>(), u_full, ctx->u_o0, ctx->u_no);
         k_reduce_J_lines<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_lines.as<double>());
-        if (ctx->params.anisotropic) { k_reduce_anis<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_anis.as<double>()); launches++; }
-        if (K)
+        if (anis) { k_reduce_anis<<<(unsigned)((nl + 255) / 256), 256, 0, ctx->stream>>>(m, ch->o0, no, sc.u, ctx->J_anis.as<double>()); launches++; }
+        if (shortchar) {
+            const unsigned nb = (unsigned)((nl + 127) / 128);
+            if (approx == APPROX_NONE) k_reduce_lambda_sc<APPROX_NONE><<<nb, 128, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.offV, ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
+            else if (approx == APPROX_ONELINE) k_reduce_lambda_sc<APPROX_ONELINE><<<nb, 128, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.offV, ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
+            else k_reduce_lambda_sc<APPROX_CLOSELINES><<<nb, 128, 0, ctx->stream>>>(m, ch->o0, no, ctx->lens.as<uint32_t>(), sc.offV, ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>());
+        } else if (K)
             k_reduce_lambda_banded<<<(unsigned)((nl + 127) / 128), 128, 0, ctx->stream>>>(
                 m, ch->o0, no, K, ctx->lam_cap, ctx->lens.as<uint32_t>(), sc.L, sc.offV, sc.offN, ctx->lam_list_val.as<double>(),
                 ctx->lam_list_nr.as<uint32_t>(), ctx->lam_val.as<double>(), ctx->lam_cnt.as<uint32_t>(), ctx->counters.as<unsigned long long>() + 4);
@@ -697,9 +724,17 @@ extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_be
     st.n_chunks = (uint32_t)ctx->chunks.size();
     st.n_launches = launches;
     st.paths_cached = all_cached ? 1 : 0;
-    ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true; ctx->res_anis = ctx->params.anisotropic != 0;
+    ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true; ctx->res_anis = anis;
     if (stats) *stats = st;
     return MGB_OK;
+}
+
+extern "C" int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32_t o_end, mgb_stats* stats) {
+    return run_radiation_field(ctx, approx, o_begin, o_end, stats, false, 0.0);
+}
+
+extern "C" int mgb_run_shortchar_order_0(mgb_ctx* ctx, int approx, double min_dtau, uint32_t o_begin, uint32_t o_end, mgb_stats* stats) {
+    return run_radiation_field(ctx, approx, o_begin, o_end, stats, true, min_dtau);
 }
 
 static int check_range(mgb_ctx* ctx, uint32_t o0, uint32_t o1, const char* who) {

@@ -30,6 +30,7 @@ PYBIND11_MODULE(core, m) {
         .def_readwrite("min_rel_pop_for_convergence", &Parameters::min_rel_pop_for_convergence)
         .def_readwrite("pop_prec", &Parameters::pop_prec)
         .def_readwrite("min_opacity", &Parameters::min_opacity)
+        .def_readwrite("min_dtau", &Parameters::min_dtau)
         .def_property("min_line_opacity", [](const Parameters& p) { return (double)p.min_line_opacity; }, [](Parameters& p, double v) { p.min_line_opacity = v; })
         .def_property("min_line_emissivity", [](const Parameters& p) { return (double)p.min_line_emissivity; }, [](Parameters& p, double v) { p.min_line_emissivity = v; })
         .def_readwrite("max_interpolation_diff", &Parameters::max_interpolation_diff)
@@ -139,6 +140,8 @@ PYBIND11_MODULE(core, m) {
         .def("compute_level_populations_from_stateq", &Model::compute_level_populations_from_stateq)
         .def("compute_level_populations", &Model::compute_level_populations)
         .def("compute_radiation_field_feautrier_order_2_sparse", &Model::compute_radiation_field_feautrier_order_2_sparse)
+        .def("compute_radiation_field_shortchar_order_0", &Model::compute_radiation_field_shortchar_order_0)
+        .def("compute_level_populations_shortchar", &Model::compute_level_populations_shortchar)
         .def("compute_Jeff_sparse", &Model::compute_Jeff_sparse)
         .def("compute_radiation_field_feautrier_order_2_anis", &Model::compute_radiation_field_feautrier_order_2_anis)
         .def("get_J_anis", [](const Model& s, Size l) { /* (J, J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im) of species l, each [npoints][nrad] */

@@ -49,6 +49,7 @@ struct Parameters { // reference src/model/parameters/parameters.hpp:66-124 (the
     Size n_off_diag = 0;
     Real max_width_fraction = 0.35, convergence_fraction = 0.995, min_rel_pop_for_convergence = 1.0e-10, pop_prec = 1.0e-6;
     Real min_opacity = 1.0e-26;
+    Real min_dtau = 1.0e-15; // lower bound of a segment's optical depth in the short-characteristics solver (solver.tpp:1608)
     LD min_line_opacity = 1.0e-13, min_line_emissivity = 1.0e-50;
     Real max_interpolation_diff = 1.4, max_distance_opacity_contribution = 10.0;
     Real population_inversion_fraction = -1.0;
@@ -650,6 +651,10 @@ class Model {
                                      "lineProducingSpecies.tpp:377-581); the host layer solves the block-diagonal case only. The banded Lambda "
                                      "lists are available from the C ABI (mgb_get_lambda_lists).");
         run_radiation_field(true);
+        fetch_J_and_lambda();
+        return 0;
+    }
+    void fetch_J_and_lambda() {
         const Size L = nlines();
         J.resize((size_t)npoints * nfreqs);
         std::vector<double> lam((size_t)npoints * L);
@@ -665,6 +670,14 @@ class Model {
                     ls.lambda_cnt[(size_t)p * nrad + k] = cnt[(size_t)p * L + nrad_cum[l] + k];
                 }
         }
+    }
+    // ---- Model::compute_radiation_field_shortchar_order_0 (model.cpp:313-349; Solver::solve_shortchar_order_0, solver.tpp:150-235):
+    //      J and the local Lambda element from the short-characteristics solver (mgb_run_shortchar_order_0) ----
+    int compute_radiation_field_shortchar_order_0() {
+        shortchar = true;
+        try { run_radiation_field(true); } catch (...) { shortchar = false; throw; }
+        shortchar = false;
+        fetch_J_and_lambda();
         return 0;
     }
     // ---- Model::compute_radiation_field_feautrier_order_2_sparse (model.cpp:474-510; Solver::solve_feautrier_order_2_sparse,
@@ -811,6 +824,14 @@ class Model {
     int compute_level_populations(const bool use_Ng_acceleration, const long max_niterations) { return level_population_loop(use_Ng_acceleration, max_niterations, false); }
     // ---- Model::compute_level_populations_sparse (model.cpp:756-850): the same loop over the memory-sparse radiation field ----
     int compute_level_populations_sparse(const bool use_Ng_acceleration, const long max_niterations) { return level_population_loop(use_Ng_acceleration, max_niterations, true); }
+    // ---- Model::compute_level_populations_shortchar (model.cpp:859-953): the same loop over the short-characteristics radiation field ----
+    int compute_level_populations_shortchar(const bool use_Ng_acceleration, const long max_niterations) {
+        shortchar = true;
+        int it;
+        try { it = level_population_loop(use_Ng_acceleration, max_niterations, false); } catch (...) { shortchar = false; throw; }
+        shortchar = false;
+        return it;
+    }
     int level_population_loop(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
         if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
         if (device_level_populations) return level_population_loop_device(use_Ng_acceleration, max_niterations, sparse);
@@ -827,6 +848,7 @@ class Model {
                 some_not_converged = false;
                 const double t0 = now();
                 if (sparse) { compute_radiation_field_feautrier_order_2_sparse(); compute_Jeff_sparse(); }
+                else if (shortchar) { run_radiation_field(true); fetch_J_and_lambda(); compute_Jeff(); }
                 else { compute_radiation_field_feautrier_order_2(); compute_Jeff(); }
                 const double t1 = now();
                 if (sparse) compute_level_populations_from_stateq_sparse(); else compute_level_populations_from_stateq();
@@ -847,7 +869,7 @@ class Model {
     // unchanged; each step calls the device twin of the Lines:: / LineProducingSpecies:: routine the reference calls. Host copies of
     // populations, Jlin/Jeff, the line state, J (or lspec.J) and Lambda are refreshed when the loop ends.
     int level_population_loop_device(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
-        if (parameters.n_off_diag) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update."); /* block-diagonal only */
+        if (parameters.n_off_diag && !shortchar) throw std::runtime_error("parameters->n_off_diag != 0 so cannot use sparse update."); /* block-diagonal only */
         sync_static(true);
         sync_levelpop();
         int iteration = 0, iteration_normal = 0;
@@ -978,7 +1000,7 @@ class Model {
     mgb_ctx* ctx = nullptr;
     bool dirty_geometry = true, dirty_thermo = true, dirty_lines = true, dirty_freqs = true, dirty_species = true, comm_dirty = false;
     std::string comm_id;
-    bool have_partition = false, anisotropic = false;
+    bool have_partition = false, anisotropic = false, shortchar = false;
     unsigned long state_serial = 1, state_uploaded = 0; // host emissivity / opacity / inverse_width changed <-> last upload for the imager
     // One radiation-field pass on this rank's origins (+ the all-gather): Solver::solve_feautrier_order_2[_sparse] (solver.tpp:297-363, 458-540).
     // upload_state: the host's emissivity / opacity / inverse_width go up first (the host-twin path); otherwise the device table is current.
@@ -994,7 +1016,8 @@ class Model {
             check(mgb_partition_balanced(ctx, nranks, rank, &o_begin, &o_end), "mgb_partition_balanced");
             have_partition = true;
         }
-        const int rc = mgb_run_feautrier_order_2(ctx, approx(), o_begin, o_end, &last_stats);
+        const int rc = shortchar ? mgb_run_shortchar_order_0(ctx, approx(), parameters.min_dtau, o_begin, o_end, &last_stats)
+                                 : mgb_run_feautrier_order_2(ctx, approx(), o_begin, o_end, &last_stats);
         if (nranks > 1) { /* agree before the collective: a rank that failed must not leave its peers inside the all-gather */
             int all = rc;
             check(mgb_comm_agree(ctx, rc, &all), "mgb_comm_agree");

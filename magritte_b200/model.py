@@ -7,7 +7,7 @@ compute_level_populations(use_Ng_acceleration, max_niterations), compute_image_n
 import numpy as np
 
 PARAMETER_NAMES = ("n_off_diag", "max_width_fraction", "convergence_fraction", "min_rel_pop_for_convergence", "pop_prec", "min_opacity",
-                   "min_line_opacity", "max_interpolation_diff", "max_distance_opacity_contribution", "population_inversion_fraction",
+                   "min_line_opacity", "max_interpolation_diff", "max_distance_opacity_contribution", "population_inversion_fraction", "min_dtau",
                    "use_adaptive_Ng_acceleration", "adaptive_Ng_acceleration_use_max_criterion", "Ng_acceleration_mem_limit",
                    "adaptive_Ng_acceleration_min_order", "Ng_acceleration_remove_N_its", "one_line_approximation",
                    "sum_opacity_emissivity_over_all_lines")

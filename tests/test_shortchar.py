@@ -63,7 +63,7 @@ def test_gpu_shortchar_against_oracle_and_reference(name):
         ctx.set_model(flat)
         st = ctx.run_shortchar(approx_of(flat["params"]), store_u=True)
         J, u = ctx.get_J(), ctx.get_u()
-        val, cnt = ctx.get_lambda_diag()
+        val, cnt = ctx.get_lambda()
     finally:
         ctx.close()
     assert st.n_launches > 0
@@ -84,17 +84,61 @@ def test_gpu_shortchar_origin_ranges_and_other_approximations():
     ctx = cabi.Context(0)
     try:
         ctx.set_model(flat)
-        for approx in (cabi.APPROX_NONE, cabi.APPROX_ONELINE, cabi.APPROX_CLOSELINES):
+        for approx in (0, 1, 2):
             o = orc.Oracle(flat, approx=approx, store_u=False)
             o.shortchar()
             ctx.run_shortchar(approx)
             J = ctx.get_J()
-            val, cnt = ctx.get_lambda_diag()
+            val, cnt = ctx.get_lambda()
             assert np.array_equal(J, o.J), approx
             assert np.array_equal(val, o.L_val[:, :, 0]) and np.array_equal(cnt, o.L_cnt), approx
         N = int(flat["npoints"])
-        ctx.run_shortchar(cabi.APPROX_CLOSELINES, (N // 3, N // 2))
+        ctx.run_shortchar(2, (N // 3, N // 2))
         Jp = ctx.get_J()
-        assert np.array_equal(Jp[N // 3:N // 2], J[N // 3:N // 2])
+        assert Jp.shape[0] == N // 2 - N // 3 and np.array_equal(Jp, J[N // 3:N // 2])
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["c2_vanzadelhoff", "wind3d_small", "wind3d_spiral_2spec"])
+@pytest.mark.parametrize("device_lp", [True, False])
+def test_gpu_host_model_shortchar_radiation_field_and_one_iteration(name, device_lp):
+    """Model::compute_radiation_field_shortchar_order_0 and ONE iteration of compute_level_populations_shortchar through the C++ host
+    Model: J bit for bit; populations (populations criterion) and Jeff of the interior points against the compiled reference (a
+    point's statistical equilibrium reads its own Lambda element only, and the boundary points' elements are undefined there)."""
+    from test_gpu_levelpop import prepared
+    from test_host_model import assert_populations_close
+    g = load_shortchar(name)
+    m, flat, ref, lp = prepared(name)
+    m.device_level_populations = device_lp
+    m.compute_radiation_field_shortchar_order_0()
+    assert np.array_equal(m.get_J(), g["J"])
+    m.mutable_parameters().use_adaptive_Ng_acceleration = False
+    assert m.compute_level_populations_shortchar(False, 1) == 1
+    it = g["interior"]
+    for l in range(len(lp["species"])):
+        got = m.get_population(l)
+        want = g[f"iter1_population_{l}"].reshape(got.shape)
+        assert_populations_close(got[it], want[it], np.asarray(m.get_population_tot(l))[it], name)
+        Jeff = np.asarray(m.get_Jeff(l))
+        assert util.relerr(Jeff[it], g[f"iter1_Jeff_{l}"].reshape(Jeff.shape)[it]) <= 1e-12
+
+
+@pytest.mark.gpu
+def test_gpu_facade_shortchar():
+    """The magritte.core surface: compute_radiation_field_shortchar_order_0 fills radiation.J and the Lambda lists."""
+    import magritte_b200.core_compat as core
+    from magritte_b200 import modelbuild as mb
+    name = "velgrad_1d"
+    g = load_shortchar(name)
+    m = mb.build(core, core.IoPython("mem", "sc_facade"), "sc_facade", util.small_specs()[name])
+    mb.prepare(m)
+    assert m.compute_radiation_field_shortchar_order_0() == 0
+    assert np.array_equal(np.array(m.radiation.J), g["J"])
+    it = np.flatnonzero(g["interior"])
+    Ls = m.lines.lineProducingSpecies[0].Lambda.Ls
+    nr = m.lines.lineProducingSpecies[0].Lambda.nr
+    for p in it[:50]:
+        for k in range(g["lambda_val"].shape[1]):
+            assert nr[p][k] == [p] and Ls[p][k] == [g["lambda_val"][p, k]]
