@@ -211,6 +211,15 @@ int mgb_image_optical_depth(mgb_ctx* ctx, int approx, int dimension, const doubl
  * column [nrays][o_end-o_begin] (rows of Model::column, host). Needs the geometry only. ms_kernel (may be NULL): device time
  * of the kernel. A ray that dead-ends inside the model stops there (the reference would index density[npoints]). */
 int mgb_set_column(mgb_ctx* ctx, const double* density, uint32_t o_begin, uint32_t o_end, double* column, float* ms_kernel);
+/* mgb_set_column without any device allocation. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it). Same inputs, outputs
+ * and results as mgb_set_column (host density [npoints] in, host column [nrays][o_end-o_begin] out), but the density and the column
+ * block are staged through a file-scope static device array of 4 Mi doubles (32 MiB, held by every GPU that loads the library until
+ * the process exits) instead of per-call buffers: the call makes no cudaMalloc / cudaFree and uses no allocating library routine.
+ * LIMIT: npoints (rounded up to a multiple of 32) + nrays * (o_end - o_begin) <= 4 194 304, else MGB_EINVAL with the sizes in
+ * mgb_last_error -- split the origin range or use mgb_set_column. All calls in the process share the array per device: calls that
+ * overlap on one GPU race and must be serialised by the caller. Synchronous. */
+int mgb_set_column_noalloc(mgb_ctx* ctx, const double* density, uint32_t o_begin, uint32_t o_end, double* column);
 
 /* ---- multi-GPU: origin partition + NCCL all-gather ---------------------------- */
 /* 128-byte ncclUniqueId made on rank 0 and distributed by the host application. */

@@ -21,7 +21,7 @@ EXPORTS = [
     "mgb_allgather_results", "mgb_comm_destroy", "mgb_comm_agree", "mgb_set_radiation_field", "mgb_lp_set_parameters", "mgb_lp_set_species", "mgb_lp_add_collision_partner", "mgb_lp_set_abundance",
     "mgb_lp_set_populations", "mgb_lp_get_populations", "mgb_lp_refresh_line_state", "mgb_lp_get_line_state", "mgb_lp_compute_Jeff", "mgb_lp_get_Jeff",
     "mgb_lp_update_statistical_equilibrium", "mgb_lp_ng_gram", "mgb_lp_ng_combine", "mgb_lp_finish_update", "mgb_lp_trial_convergence",
-    "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_get_J_anis", "mgb_image_optical_depth", "mgb_set_column",
+    "mgb_image_feautrier_order_2", "mgb_trace_dump", "mgb_selftest_libm", "mgb_measure_fp64_peak", "mgb_selftest_ddiv", "mgb_get_J_lines", "mgb_get_J_anis", "mgb_image_optical_depth", "mgb_set_column", "mgb_set_column_noalloc",
 ]
 
 
@@ -189,6 +189,15 @@ class Context:
         self._check(self.lib.mgb_set_column(self._ctx, prho, C.c_uint32(o0), C.c_uint32(o1), col.ctypes.data_as(C.c_void_p),
                                             C.byref(ms)), "mgb_set_column")
         return (col, ms.value) if with_time else col
+
+    def set_column_noalloc(self, density, o_range=None):
+        """mgb_set_column_noalloc: set_column staged through the library's static device array (no device allocation in the call)."""
+        rho, prho = _p(density, np.float64)
+        o0, o1 = o_range or (0, self.npoints)
+        col = np.empty((self.nrays, max(o1 - o0, 0)))
+        self._check(self.lib.mgb_set_column_noalloc(self._ctx, prho, C.c_uint32(o0), C.c_uint32(o1), col.ctypes.data_as(C.c_void_p)),
+                    "mgb_set_column_noalloc")
+        return col
 
     def image(self, approx, dimension, ray_dir, nx, ny, nu, pix_range=None, optical_depth=False):
         """mgb_image_feautrier_order_2 (or mgb_image_optical_depth): nu is [nfreqs] (common bins) or [npoints][nfreqs].
