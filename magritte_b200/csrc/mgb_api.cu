@@ -7,7 +7,10 @@
 #include <cub/device/device_scan.cuh>
 
 #include "mgb_ctx.h"
-#include "mgb_solve2.cuh"
+#ifndef MGB_DEFAULT_SOLVE_KERNEL
+#define MGB_DEFAULT_SOLVE_KERNEL 1
+#endif
+#include "mgb_solve3.cuh"
 #include "mgb_shortchar.cuh"
 
 using namespace mgb;
@@ -466,10 +469,23 @@ cudaError_t launch_solve_v2(mgb_ctx* ctx, const PathView& pv, const ScratchView&
                                                                                ctx->lines_per_warp2);
     return cudaGetLastError();
 }
+// MGB_SOLVE_KERNEL=3: k_solve3 (mgb_solve3.cuh: k_solve's work items, straight-line common step, range-free erff)
+template <int APPROX>
+cudaError_t launch_solve_v3(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
+    const size_t nitems = (size_t)pv.no * ctx->m.hnrays * nchunks_f;
+    const size_t blocks = (nitems + kSolve3Warps - 1) / kSolve3Warps;
+    const size_t smem   = kSolve3Warps * solve_smem_per_warp(ctx->lines_per_warp);
+    cudaError_t e = cudaFuncSetAttribute(k_solve3<APPROX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_solve3<APPROX><<<(unsigned)blocks, 32 * kSolve3Warps, smem, ctx->stream>>>(ctx->m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f,
+                                                                               ctx->lines_per_warp);
+    return cudaGetLastError();
+}
 template <int APPROX>
 cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
     if (sc.K) return launch_solve2<APPROX, true>(ctx, pv, sc, nchunks_f);
-    return ctx->solve_v2 ? launch_solve_v2<APPROX>(ctx, pv, sc) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
+    if (ctx->solve_v2 == 3) return launch_solve_v3<APPROX>(ctx, pv, sc, nchunks_f);
+    return ctx->solve_v2 == 2 ? launch_solve_v2<APPROX>(ctx, pv, sc) : launch_solve2<APPROX, false>(ctx, pv, sc, nchunks_f);
 }
 template <int APPROX>
 cudaError_t launch_shortchar(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f, double min_dtau) {
@@ -642,7 +658,8 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
     {
         const char* v2 = getenv("MGB_SOLVE_V2");
-        ctx->solve_v2 = v2 && v2[0] == '1';
+        const char* vk = getenv("MGB_SOLVE_KERNEL"); /* 1: k_solve, 2: k_solve2, 3: k_solve3 */
+        ctx->solve_v2 = (vk && vk[0] >= '1' && vk[0] <= '3') ? vk[0] - '0' : ((v2 && v2[0] == '1') ? 2 : MGB_DEFAULT_SOLVE_KERNEL);
     }
     const bool lambda2 = !K && !shortchar; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
     if (shortchar) MGB_CUDA(ctx, ctx->scratch_offV.ensure(16 * (size_t)m.hnrays * max_no * m.nfreqs)); /* the two half-ray factors of each (rr, o, f) */

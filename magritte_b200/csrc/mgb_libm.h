@@ -23,6 +23,14 @@
 // erff, expm1f) and a 2^32-point lattice for powf; on the GPU, mgb_selftest_libm() runs the device
 // build against host-libm results (tests/test_gpu_parity.py::test_device_libm_bit_exact).
 //
+// Notices of the restated third-party sources (algorithms, tables and coefficients; the code below is this project's):
+//   * expf / logf / powf kernels and their data tables: Arm Optimized Routines, Copyright (c) 2017-2018, Arm Limited,
+//     SPDX-License-Identifier: MIT (as imported into glibc 2.28+ under the GNU LGPL v2.1 or later, sysdeps/ieee754/flt-32/e_expf.c,
+//     e_logf.c, e_powf.c, e_exp2f_data.c, e_logf_data.c, e_powf_log2_data.c).
+//   * erff / expm1f: fdlibm s_erf.c / s_expm1.c float ports. "Copyright (C) 1993 by Sun Microsystems, Inc. All rights reserved.
+//     Developed at SunPro, a Sun Microsystems, Inc. business. Permission to use, copy, modify, and distribute this software is
+//     freely granted, provided that this notice is preserved."
+//
 // The translation unit that includes this must be compiled with nvcc -fmad=false (no implicit
 // contraction); -prec-div / -prec-sqrt / no -ftz are the nvcc defaults.
 #pragma once
@@ -345,4 +353,75 @@ MGB_LIBM_FN float mgb_erff(float x) {
     r = MGB_ERFF_EXPF(-z * z - 0.5625f) * MGB_ERFF_EXPF((z - x) * (z + x) + R / S);
     if (hx >= 0) return one - r / x;
     return r / x - one;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// erff without the range branches (the solve kernel's large-shift path evaluates two erff per segment and bin, and the lanes of a
+// warp fall into different |x| ranges: the branchy routine above ran at 12 of 32 lanes). Same arithmetic, same bits:
+//   * the four rational approximations share one Horner evaluation on a per-range coefficient row, rows padded with LEADING zeros
+//     (c + t * 0 = c exactly for finite t, so the padded steps reproduce the shorter polynomial bit for bit);
+//   * the variable is x*x, |x| - 1 or 1 / (x*x) by range; the exp() factor of the two outer ranges is evaluated by every lane on its
+//     own (possibly meaningless) argument with the special-case-free expf kernel and selected at the end;
+//   * |x| >= 6 gives +-(1 - tiny) = +-1; inf, NaN and |x| < 2^-28 go to mgb_erff.
+// tests/test_libm_host.py compares it with the box's erff over all 2^32 inputs.
+MGB_LIBM_TAB float mgb_erff_rows[4][16] = {
+    /* |x| < 0.84375: pp0..pp4, qq1..qq5 */
+    {1.2837916613e-01f, -3.2504209876e-01f, -2.8481749818e-02f, -5.7702702470e-03f, -2.3763017452e-05f, 0.0f, 0.0f, 0.0f,
+     3.9791721106e-01f, 6.5022252500e-02f, 5.0813062117e-03f, 1.3249473704e-04f, -3.9602282413e-06f, 0.0f, 0.0f, 0.0f},
+    /* 0.84375 <= |x| < 1.25: pa0..pa6, qa1..qa6 */
+    {-2.3621185683e-03f, 4.1485610604e-01f, -3.7220788002e-01f, 3.1834661961e-01f, -1.1089469492e-01f, 3.5478305072e-02f,
+     -2.1663755178e-03f, 0.0f, 1.0642088205e-01f, 5.4039794207e-01f, 7.1828655899e-02f, 1.2617121637e-01f, 1.3637083583e-02f,
+     1.1984500103e-02f, 0.0f, 0.0f},
+    /* 1.25 <= |x| < 1/0.35: ra0..ra7, sa1..sa8 */
+    {-9.8649440333e-03f, -6.9385856390e-01f, -1.0558626175e+01f, -6.2375331879e+01f, -1.6239666748e+02f, -1.8460508728e+02f,
+     -8.1287437439e+01f, -9.8143291473e+00f, 1.9651271820e+01f, 1.3765776062e+02f, 4.3456588745e+02f, 6.4538726807e+02f,
+     4.2900814819e+02f, 1.0863500214e+02f, 6.5702495575e+00f, -6.0424413532e-02f},
+    /* 1/0.35 <= |x| < 6: rb0..rb6, sb1..sb7 */
+    {-9.8649431020e-03f, -7.9928326607e-01f, -1.7757955551e+01f, -1.6063638306e+02f, -6.3756646729e+02f, -1.0250950928e+03f,
+     -4.8351919556e+02f, 0.0f, 3.0338060379e+01f, 3.2579251099e+02f, 1.5367296143e+03f, 3.1998581543e+03f, 2.5530502930e+03f,
+     4.7452853394e+02f, -2.2440952301e+01f, 0.0f}};
+#ifndef MGB_ERFF_ROW /* where a coefficient row is read from (a device build may stage the table in shared memory) */
+#define MGB_ERFF_ROW(r) mgb_erff_rows[r]
+#endif
+
+// __expf's table + polynomial kernel without its special cases: the bits of mgb_expf(x) for |x| < 88; any other input gives some
+// float without trapping (the callers discard it).
+MGB_LIBM_FN float mgb_expf_kernel(float x) {
+    const double xd    = (double)x;
+    const double SHIFT = 0x1.8p+52, InvLn2N = 0x1.71547652b82fep+5;
+    double kd          = MGB_FMA(InvLn2N, xd, SHIFT);
+    const uint64_t ki  = (uint64_t)MGB_D2LL(kd);
+    kd                 = kd - SHIFT;
+    const double r     = MGB_FMA(InvLn2N, xd, -kd);
+    return mgb_exp2f_core(r, ki, 0, 0x1.c6af84b912394p-20, 0x1.ebfce50fac4f3p-13, 0x1.62e42ff0c52d6p-6);
+}
+
+// The straight-line part: valid for 2^-28 <= |x| < inf (the caller routes the rest to mgb_erff).
+MGB_LIBM_FN float mgb_erff_main(float x) {
+    const float erx  = 8.4506291151e-01f;
+    const int32_t hx = MGB_F2I(x), ix = hx & 0x7fffffff;
+    const int far_   = ix >= 0x40c00000; /* |x| >= 6: the result is +-(1 - tiny); the arithmetic below runs on a harmless stand-in */
+    const float ax   = far_ ? 3.0f : MGB_I2F(ix);
+    const int r      = (ix < 0x3f580000) ? 0 : (ix < 0x3fa00000) ? 1 : (ix < 0x4036DB6E) ? 2 : 3;
+    const float xx   = ax * ax;
+    const float t    = (r == 0) ? xx : (r == 1) ? ax - 1.0f : 1.0f / xx;
+    const float* c   = MGB_ERFF_ROW(r);
+    float P = c[7], Q = c[15];
+    P = c[6] + t * P; P = c[5] + t * P; P = c[4] + t * P; P = c[3] + t * P; P = c[2] + t * P; P = c[1] + t * P; P = c[0] + t * P;
+    Q = c[14] + t * Q; Q = c[13] + t * Q; Q = c[12] + t * Q; Q = c[11] + t * Q; Q = c[10] + t * Q; Q = c[9] + t * Q; Q = c[8] + t * Q;
+    Q = 1.0f + t * Q;
+    const float y  = P / Q;
+    const float z  = MGB_I2F(MGB_F2I(ax) & (int32_t)0xfffff000);
+    const float e1 = mgb_expf_kernel(-z * z - 0.5625f), e2 = mgb_expf_kernel((z - ax) * (z + ax) + y);
+    const float rr = e1 * e2;
+    float big      = 1.0f - rr / ax;
+    big            = far_ ? 1.0f : big; /* one - tiny */
+    const float mag = (r == 1) ? erx + y : big;
+    return (r == 0) ? x + x * y : ((hx < 0) ? -mag : mag);
+}
+
+MGB_LIBM_FN float mgb_erff_u(float x) {
+    const int32_t ix = MGB_F2I(x) & 0x7fffffff;
+    if (ix >= 0x7f800000 || ix < 0x31800000) return mgb_erff(x);
+    return mgb_erff_main(x);
 }

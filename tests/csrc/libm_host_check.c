@@ -1,5 +1,5 @@
 /* Exhaustive host check of magritte_b200/csrc/mgb_libm.h against the box's own libm (test infrastructure).
- * usage: libm_host_check <fn> [stride]   fn in expf logf erff expm1f powf; prints mismatch count. */
+ * usage: libm_host_check <fn> [stride]   fn in expf logf erff erff_u expm1f powf; prints mismatch count. */
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
@@ -27,7 +27,7 @@ int main(int argc, char** argv) {
             for (int j = 0; j < ny; j++) { n++; if (!same(mgb_powf(x, ys[j]), powf(x, ys[j]))) { bad++; if (!have) { have = 1; first_bad = b; } } }
         }
     } else {
-        int which = !strcmp(fn, "expf") ? 0 : !strcmp(fn, "logf") ? 1 : !strcmp(fn, "erff") ? 2 : 3;
+        int which = !strcmp(fn, "expf") ? 0 : !strcmp(fn, "logf") ? 1 : !strcmp(fn, "erff") ? 2 : !strcmp(fn, "erff_u") ? 4 : 3;
 #pragma omp parallel for reduction(+ : bad, n) schedule(static)
         for (uint64_t u = 0; u < (1ull << 32); u += stride) {
             float x; uint32_t b = (uint32_t)u; memcpy(&x, &b, 4);
@@ -36,6 +36,7 @@ int main(int argc, char** argv) {
             case 0: a = mgb_expf(x); r = expf(x); break;
             case 1: a = mgb_logf(x); r = logf(x); break;
             case 2: a = mgb_erff(x); r = erff(x); break;
+            case 4: a = mgb_erff_u(x); r = erff(x); break;
             default: a = mgb_expm1f(x); r = expm1f(x); break;
             }
             n++;

@@ -23,7 +23,7 @@ def checker(tmp_path_factory):
     return exe
 
 
-@pytest.mark.parametrize("fn,stride", [("expf", 1), ("logf", 1), ("erff", 1), ("expm1f", 1), ("powf", 257)])
+@pytest.mark.parametrize("fn,stride", [("expf", 1), ("logf", 1), ("erff", 1), ("erff_u", 1), ("expm1f", 1), ("powf", 257)])
 def test_bit_exact_against_host_libm(checker, fn, stride):
     out = subprocess.run([checker, fn, str(stride)], capture_output=True, text=True)
     assert out.returncode == 0 and "mismatches=0" in out.stdout, out.stdout + out.stderr
