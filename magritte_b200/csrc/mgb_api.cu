@@ -5,12 +5,13 @@
 #include <numeric>
 
 #include <cub/device/device_scan.cuh>
+#include <cub/iterator/transform_input_iterator.cuh>
 
 #include "mgb_ctx.h"
 #ifndef MGB_DEFAULT_SOLVE_KERNEL
 #define MGB_DEFAULT_SOLVE_KERNEL 1
 #endif
-#include "mgb_solve3.cuh"
+#include "mgb_solve4.cuh"
 #include "mgb_shortchar.cuh"
 
 using namespace mgb;
@@ -135,6 +136,16 @@ extern "C" int mgb_set_geometry(mgb_ctx* ctx, uint32_t npoints, const double* po
     MGB_TRY(upload(ctx, ctx->dir, direction, sizeof(double) * 3 * nrays));
     MGB_TRY(upload(ctx, ctx->weight, weight, sizeof(double) * nrays));
     MGB_TRY(upload(ctx, ctx->antipod, antipod, sizeof(uint32_t) * nrays));
+    {   /* which side of a ray pair a half ray is (k_large: orientation of the generic line integral): 0 = the pair's ray rr, 1 = its antipode */
+        std::vector<uint8_t> side(nrays, 2);
+        ctx->side_ok = true;
+        for (uint32_t rr = 0; rr < nrays / 2; rr++) {
+            if (side[rr] == 1 || antipod[rr] < nrays / 2) ctx->side_ok = false;
+            side[rr] = 0; side[antipod[rr]] = 1;
+        }
+        for (uint32_t r = 0; r < nrays; r++) if (side[r] == 2) { ctx->side_ok = false; side[r] = 1; }
+        MGB_TRY(upload(ctx, ctx->side_of, side.data(), nrays));
+    }
     MGB_TRY(upload(ctx, ctx->p2b, point2boundary, sizeof(uint32_t) * npoints));
     MGB_TRY(upload(ctx, ctx->bcond, boundary_condition, sizeof(int32_t) * nboundary));
     MGB_TRY(upload(ctx, ctx->btemp, boundary_temperature, sizeof(double) * nboundary));
@@ -481,6 +492,121 @@ cudaError_t launch_solve_v3(mgb_ctx* ctx, const PathView& pv, const ScratchView&
                                                                                ctx->lines_per_warp);
     return cudaGetLastError();
 }
+// MGB_SOLVE_KERNEL=4: the streaming pipeline of mgb_solve4.cuh on one path chunk. The chunk's origins are taken in sub-ranges whose
+// records fit the record budget (MGB_REC_BYTES, default 40 GB for the 80-byte records; the line integrals of the large-shift
+// segments come on top, 24 * nquads bytes each).
+struct CastU64 {
+    __host__ __device__ unsigned long long operator()(uint32_t v) const { return v; }
+};
+template <int APPROX>
+int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, const PathChunk* ch, uint32_t nchunks_f, uint32_t& launches) {
+    const DevModel& m = ctx->m;
+    if (!ctx->side_ok) return ctx->fail(MGB_EUNSUPPORTED, "MGB_SOLVE_KERNEL=4 needs antipod[rr] >= nrays/2 for every rr < nrays/2");
+    static const unsigned long long budget = [] {
+        const char* e = getenv("MGB_REC_BYTES");
+        const unsigned long long v = e ? strtoull(e, nullptr, 10) : 0ull;
+        return v ? v : (40ull << 30);
+    }();
+    const uint32_t no = pv.no;
+    const size_t lists_per_o = (size_t)m.nrays * m.nlines;
+    auto est_bytes = [&](uint32_t ol) { /* records of one origin: steps x lines (x 1.3 for sub-steps) + one origin record per list */
+        const unsigned long long so = ctx->origin_steps[ch->o0 + ol - ctx->lens_o0];
+        return (unsigned long long)(80.0 * 1.3 * (double)so * m.nlines) + 80ull * lists_per_o;
+    };
+    MGB_CUDA(ctx, ctx->rec_lcount.ensure(8));
+    uint32_t a = 0;
+    while (a < no) {
+        uint32_t b = a;
+        unsigned long long est = 0;
+        while (b < no && (b == a || est + est_bytes(b) <= budget)) { est += est_bytes(b); b++; }
+        unsigned long long nrec = 0, nelem = 0;
+        RecView rv{};
+        DenseView dv{};
+        for (;;) { /* elements and records of the range; halve the range when the records would not fit */
+            const uint32_t nhr = (b - a) * m.nrays;
+            MGB_CUDA(ctx, ctx->rec_cnt.ensure(4 * ((size_t)nhr + 1)));
+            MGB_CUDA(ctx, ctx->rec_eoff.ensure(8 * ((size_t)nhr + 1)));
+            EventTimer t0(ctx->stream);
+            t0.start();
+            k_ecount<<<(nhr + 1 + 255) / 256, 256, 0, ctx->stream>>>(nhr, m.nrays, m.nlines, pv.o0 + a, pv.len, ctx->rec_cnt.as<uint32_t>());
+            MGB_CUDA(ctx, cudaGetLastError());
+            size_t tmp = 0;
+            {
+                cub::TransformInputIterator<unsigned long long, CastU64, const uint32_t*> in(ctx->rec_cnt.as<uint32_t>(), CastU64());
+                cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, ctx->rec_eoff.as<unsigned long long>(), (int64_t)nhr + 1, ctx->stream);
+                MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+                MGB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, in, ctx->rec_eoff.as<unsigned long long>(), (int64_t)nhr + 1, ctx->stream));
+            }
+            MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream)); /* the context's stream does not synchronise with the default stream's copy */
+            MGB_CUDA(ctx, cudaMemcpy(&nelem, ctx->rec_eoff.as<unsigned long long>() + nhr, 8, cudaMemcpyDeviceToHost));
+            MGB_CUDA(ctx, ctx->rec_ni.ensure(4 * ((size_t)nelem + 1)));
+            MGB_CUDA(ctx, ctx->rec_base.ensure(8 * ((size_t)nelem + 1)));
+            MGB_CUDA(ctx, cudaMemsetAsync(ctx->rec_ni.as<uint32_t>() + nelem, 0, 4, ctx->stream));
+            dv.eoff = ctx->rec_eoff.as<unsigned long long>(); dv.ni = ctx->rec_ni.as<uint32_t>(); dv.base = ctx->rec_base.as<unsigned long long>();
+            k_ni<<<(unsigned)(((size_t)nhr * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, a, b - a, dv);
+            MGB_CUDA(ctx, cudaGetLastError());
+            {
+                cub::TransformInputIterator<unsigned long long, CastU64, const uint32_t*> in(ctx->rec_ni.as<uint32_t>(), CastU64());
+                cub::DeviceScan::ExclusiveSum(nullptr, tmp, in, ctx->rec_base.as<unsigned long long>(), (int64_t)nelem + 1, ctx->stream);
+                MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+                MGB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, in, ctx->rec_base.as<unsigned long long>(), (int64_t)nelem + 1, ctx->stream));
+            }
+            ctx->ms_v4[0] += t0.stop();
+            launches += 4;
+            MGB_CUDA(ctx, cudaMemcpy(&nrec, ctx->rec_base.as<unsigned long long>() + nelem, 8, cudaMemcpyDeviceToHost));
+            if (nrec * 80ull > budget + budget / 4 && b - a > 1) { b = a + (b - a) / 2; continue; }
+            break;
+        }
+        const size_t nlists = (size_t)(b - a) * lists_per_o;
+        MGB_CUDA(ctx, ctx->rec_off.ensure(8 * (nlists + 1)));
+        MGB_CUDA(ctx, ctx->rec.ensure(64 * (size_t)nrec));
+        MGB_CUDA(ctx, ctx->rec_pts.ensure(16 * (size_t)nrec));
+        rv.ola = a; rv.nob = b - a; rv.off = ctx->rec_off.as<unsigned long long>(); rv.lcount = ctx->rec_lcount.as<unsigned long long>();
+        rv.rec = ctx->rec.as<double>(); rv.pts = ctx->rec_pts.as<double2>();
+        unsigned long long nlarge = 0;
+        {
+            EventTimer t1(ctx->stream);
+            t1.start();
+            MGB_CUDA(ctx, cudaMemsetAsync(ctx->rec_lcount.p, 0, 8, ctx->stream));
+            k_off<<<(unsigned)((nlists + 1 + 255) / 256), 256, 0, ctx->stream>>>(m, pv, a, b - a, dv, nelem, ctx->rec_off.as<unsigned long long>());
+            MGB_CUDA(ctx, cudaGetLastError());
+            k_fill<<<(unsigned)(((size_t)(b - a) * m.nrays * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, rv, dv);
+            MGB_CUDA(ctx, cudaGetLastError());
+            ctx->ms_v4[0] += t1.stop();
+            launches += 2;
+            MGB_CUDA(ctx, cudaMemcpy(&nlarge, ctx->rec_lcount.p, 8, cudaMemcpyDeviceToHost));
+        }
+        {
+            EventTimer t2(ctx->stream);
+            t2.start();
+            if (nlarge) {
+                MGB_CUDA(ctx, ctx->rec_slots.ensure(sizeof(SlotInfo) * (size_t)nlarge));
+                MGB_CUDA(ctx, ctx->rec_trip.ensure(24 * (size_t)m.nquads * (size_t)nlarge));
+                k_slots<<<(unsigned)((nlists * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, rv, ctx->side_of.as<uint8_t>(), ctx->rec_slots.as<SlotInfo>());
+                MGB_CUDA(ctx, cudaGetLastError());
+                const unsigned spb = 128 / m.nquads; /* slots per block */
+                if (!spb) return ctx->fail(MGB_EUNSUPPORTED, "MGB_SOLVE_KERNEL=4: nquads > 128");
+                k_large<APPROX><<<(unsigned)((nlarge + spb - 1) / spb), 128, 0, ctx->stream>>>(m, rv.rec, rv.pts, ctx->rec_slots.as<SlotInfo>(), nlarge, ctx->rec_trip.as<double>());
+                MGB_CUDA(ctx, cudaGetLastError());
+                launches += 2;
+            }
+            ctx->ms_v4[1] += t2.stop();
+        }
+        {
+            EventTimer t3(ctx->stream);
+            t3.start();
+            const size_t nitems = (size_t)(b - a) * m.hnrays * nchunks_f;
+            k_sweep<APPROX><<<(unsigned)((nitems + kSweepWarps - 1) / kSweepWarps), 32 * kSweepWarps, 0, ctx->stream>>>(
+                m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f, rv, ctx->rec_trip.as<double>());
+            MGB_CUDA(ctx, cudaGetLastError());
+            ctx->ms_v4[2] += t3.stop();
+            launches++;
+        }
+        a = b;
+    }
+    return MGB_OK;
+}
+
 template <int APPROX>
 cudaError_t launch_solve(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, uint32_t nchunks_f) {
     if (sc.K) return launch_solve2<APPROX, true>(ctx, pv, sc, nchunks_f);
@@ -658,8 +784,9 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
     {
         const char* v2 = getenv("MGB_SOLVE_V2");
-        const char* vk = getenv("MGB_SOLVE_KERNEL"); /* 1: k_solve, 2: k_solve2, 3: k_solve3 */
-        ctx->solve_v2 = (vk && vk[0] >= '1' && vk[0] <= '3') ? vk[0] - '0' : ((v2 && v2[0] == '1') ? 2 : MGB_DEFAULT_SOLVE_KERNEL);
+        const char* vk = getenv("MGB_SOLVE_KERNEL"); /* 1: k_solve, 2: k_solve2, 3: k_solve3, 4: the streaming pipeline (mgb_solve4.cuh) */
+        ctx->ms_v4[0] = ctx->ms_v4[1] = ctx->ms_v4[2] = 0.f;
+        ctx->solve_v2 = (vk && vk[0] >= '1' && vk[0] <= '4') ? vk[0] - '0' : ((v2 && v2[0] == '1') ? 2 : MGB_DEFAULT_SOLVE_KERNEL);
     }
     const bool lambda2 = !K && !shortchar; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
     if (shortchar) MGB_CUDA(ctx, ctx->scratch_offV.ensure(16 * (size_t)m.hnrays * max_no * m.nfreqs)); /* the two half-ray factors of each (rr, o, f) */
@@ -690,7 +817,11 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
         NvtxRange nvtx_solve("mgb: k_solve (eta/chi + Feautrier sweep)");
         EventTimer ts(ctx->stream);
         ts.start();
-        if (shortchar) {
+        if (!shortchar && !K && ctx->solve_v2 == 4) {
+            if (approx == APPROX_NONE) MGB_TRY(run_pipeline_v4<APPROX_NONE>(ctx, pv, sc, ch, nchunks_f, launches));
+            else if (approx == APPROX_ONELINE) MGB_TRY(run_pipeline_v4<APPROX_ONELINE>(ctx, pv, sc, ch, nchunks_f, launches));
+            else MGB_TRY(run_pipeline_v4<APPROX_CLOSELINES>(ctx, pv, sc, ch, nchunks_f, launches));
+        } else if (shortchar) {
             if (approx == APPROX_NONE) MGB_CUDA(ctx, launch_shortchar<APPROX_NONE>(ctx, pv, sc, nchunks_f, min_dtau));
             else if (approx == APPROX_ONELINE) MGB_CUDA(ctx, launch_shortchar<APPROX_ONELINE>(ctx, pv, sc, nchunks_f, min_dtau));
             else MGB_CUDA(ctx, launch_shortchar<APPROX_CLOSELINES>(ctx, pv, sc, nchunks_f, min_dtau));
@@ -734,6 +865,8 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
     MGB_CUDA(ctx, cudaMemcpy(c, ctx->counters.p, 40, cudaMemcpyDeviceToHost));
     st.n_entries = c[0]; st.n_large_shift = c[1];
     if (K && c[4]) return ctx->fail(MGB_ENOMEM, "banded Lambda operator: %llu list insertions exceeded the capacity %u", c[4], ctx->lam_cap);
+    if (ctx->solve_v2 == 4 && getenv("MGB_V4_DEBUG"))
+        fprintf(stderr, "[mgb v4] records %.2f ms, slots + line integrals %.2f ms, sweep %.2f ms\n", ctx->ms_v4[0], ctx->ms_v4[1], ctx->ms_v4[2]);
     st.n_steps = range_steps;
     st.n_nbs_scanned = ctx->tot_scanned; /* of the counted range */
     st.n_solves = (uint64_t)(o_end - o_begin) * m.hnrays * m.nfreqs;

@@ -118,6 +118,10 @@ struct mgb_ctx {
     bool plan_cached = false;
     mgb::PathChunk work;    // reusable chunk when paths are not cached
     mgb::DevBuf scratch_u, scratch_L, scratch_fac, counters, origin_tot, cub_tmp;
+    // streaming pipeline (mgb_solve4.cuh, MGB_SOLVE_KERNEL=4): list lengths / offsets, ray-entry records, large-shift slots and line integrals
+    mgb::DevBuf rec_cnt, rec_off, rec, rec_pts, rec_lcount, rec_slots, rec_trip, side_of, rec_eoff, rec_ni, rec_base;
+    bool side_ok = false;                             // every ray is either a `rr` (< hnrays) or the antipode of one, never both
+    float ms_v4[4] = {0, 0, 0, 0};                    // last run: records (count + fill), slots + line integrals, sweep, (spare)
     // imager: host copies of what Image::set_coordinates_projection_surface reads (boundary points in boundary order,
     // Points::center, point2boundary[0])
     std::vector<double> h_bpos;      // [nboundary][3]
