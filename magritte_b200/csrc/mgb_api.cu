@@ -511,7 +511,7 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
     const size_t lists_per_o = (size_t)m.nrays * m.nlines;
     auto est_bytes = [&](uint32_t ol) { /* records of one origin: steps x lines (x 1.3 for sub-steps) + one origin record per list */
         const unsigned long long so = ctx->origin_steps[ch->o0 + ol - ctx->lens_o0];
-        return (unsigned long long)(80.0 * 1.3 * (double)so * m.nlines) + 80ull * lists_per_o;
+        return (unsigned long long)(96.0 * 1.3 * (double)so * m.nlines) + 96ull * lists_per_o;
     };
     MGB_CUDA(ctx, ctx->rec_lcount.ensure(8));
     uint32_t a = 0;
@@ -554,7 +554,7 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
             ctx->ms_v4[0] += t0.stop();
             launches += 4;
             MGB_CUDA(ctx, cudaMemcpy(&nrec, ctx->rec_base.as<unsigned long long>() + nelem, 8, cudaMemcpyDeviceToHost));
-            if (nrec * 80ull > budget + budget / 4 && b - a > 1) { b = a + (b - a) / 2; continue; }
+            if (nrec * 96ull > budget + budget / 4 && b - a > 1) { b = a + (b - a) / 2; continue; }
             break;
         }
         const size_t nlists = (size_t)(b - a) * lists_per_o;
@@ -563,6 +563,8 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
         MGB_CUDA(ctx, ctx->rec_pts.ensure(16 * (size_t)nrec));
         rv.ola = a; rv.nob = b - a; rv.off = ctx->rec_off.as<unsigned long long>(); rv.lcount = ctx->rec_lcount.as<unsigned long long>();
         rv.rec = ctx->rec.as<double>(); rv.pts = ctx->rec_pts.as<double2>();
+        MGB_CUDA(ctx, ctx->rec_slots.ensure(sizeof(SlotInfo) * (size_t)nrec)); /* capacity: every record could end a large-shift segment */
+        rv.slots = ctx->rec_slots.as<SlotInfo>(); rv.side_of = ctx->side_of.as<uint8_t>();
         unsigned long long nlarge = 0;
         {
             EventTimer t1(ctx->stream);
@@ -580,15 +582,12 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
             EventTimer t2(ctx->stream);
             t2.start();
             if (nlarge) {
-                MGB_CUDA(ctx, ctx->rec_slots.ensure(sizeof(SlotInfo) * (size_t)nlarge));
                 MGB_CUDA(ctx, ctx->rec_trip.ensure(24 * (size_t)m.nquads * (size_t)nlarge));
-                k_slots<<<(unsigned)((nlists * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, rv, ctx->side_of.as<uint8_t>(), ctx->rec_slots.as<SlotInfo>());
-                MGB_CUDA(ctx, cudaGetLastError());
                 const unsigned spb = 128 / m.nquads; /* slots per block */
                 if (!spb) return ctx->fail(MGB_EUNSUPPORTED, "MGB_SOLVE_KERNEL=4: nquads > 128");
                 k_large<APPROX><<<(unsigned)((nlarge + spb - 1) / spb), 128, 0, ctx->stream>>>(m, rv.rec, rv.pts, ctx->rec_slots.as<SlotInfo>(), nlarge, ctx->rec_trip.as<double>());
                 MGB_CUDA(ctx, cudaGetLastError());
-                launches += 2;
+                launches += 1;
             }
             ctx->ms_v4[1] += t2.stop();
         }

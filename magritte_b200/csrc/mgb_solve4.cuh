@@ -8,13 +8,12 @@
 // that idle bandwidth for regular kernels; every per-entry number is computed by the same functions in the same operation order, so
 // the results are bit-identical to k_solve (tests/test_gpu_parity.py runs every golden through all solve kernels).
 //
-//   k_rec<count|fill>  one warp per (origin, half ray, line): the sub-stepped ray entries of that line (Solver::set_data_for_line,
-//                      solver.tpp:1057-1097; InterpHelper::get_n_interp_for_line, solver_interp_helper.tpp:55-75), lanes = entries,
+//   k_ni / k_fill      one warp per half ray, lanes = (step, line) pairs: the sub-stepped ray entries of every line (Solver::
+//                      set_data_for_line, solver.tpp:1057-1097; InterpHelper::get_n_interp_for_line, solver_interp_helper.tpp:55-75),
 //                      written as 64-byte records [shift, dz, inverse_width, emissivity, opacity, sqrtw_max, line source, flag word]
 //                      in walking order (far end -> origin, the origin's own entry last) + 16 bytes for the generic paths
 //                      (interpolation factor, the two points). The flag word holds the large-shift test of the segment that ends at
 //                      the entry (compute_source_dtau, solver.tpp:2150-2153) and, if set, the slot of that segment's line integrals.
-//   k_slots            slot -> (record, origin, line, side) table of the large-shift segments.
 //   k_large            one thread per (large-shift segment, frequency bin): compute_S_dtau_line_integrated (solver.tpp:1878-2111,
 //                      2374-2455) -> (dtau, S at the far end, S at the near end), all windows (own line, empty, generic).
 //   k_sweep            one warp per (origin, ray pair, <= 32 bins), lanes = bins: streams the records of its lines (prefetched one
@@ -35,6 +34,8 @@ struct RecView {
     double* rec;                    // [nrec][8]
     double2* pts;                   // [nrec] {interpolation factor, bits of (nr, nr_interp)}
     unsigned long long* lcount;     // slots handed out so far
+    struct SlotInfo* slots;         // [nrec] (capacity: every record could be flagged) slot -> segment
+    const uint8_t* side_of;         // [nrays] 0: the pair's ray rr, 1: its antipode
 };
 
 struct SlotInfo { unsigned long long recY; uint32_t o, lside; }; // lside = line | side << 31
@@ -61,136 +62,6 @@ __device__ __forceinline__ RecVals compute_record(const DevModel& m, uint32_t l,
         v.sline = interp_log(v.sline, ddiv(b.emissivity, b.opacity), v.factor);
     }
     return v;
-}
-
-// One warp per (origin, half ray, line). COUNT: cnt[list] = entries (0 for a half ray without steps, else sum of the sub-step counts
-// + 1 for the origin). FILL: the records. Steps are taken 32 at a time from the far end (lanes = steps), their entries 32 at a time
-// (lanes = entries).
-template <bool FILL>
-__global__ void __launch_bounds__(128) k_rec(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, RecView rv, uint32_t* __restrict__ cnt) {
-    const unsigned lane = threadIdx.x & 31;
-    const size_t list   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const size_t nlists = (size_t)rv.nob * m.nrays * m.nlines;
-    stage_exp_table();
-    if (list >= nlists) return;
-    const uint32_t l  = (uint32_t)(list % m.nlines);
-    const size_t hrl  = list / m.nlines;
-    const uint32_t r  = (uint32_t)(hrl % m.nrays);
-    const uint32_t ol = rv.ola + (uint32_t)(hrl / m.nrays);
-    const uint32_t o  = pv.o0 + ol;
-    const uint32_t len = __ldg(&pv.len[(size_t)o * m.nrays + r]);
-    if (len == 0) {
-        if (!FILL && lane == 0) cnt[list] = 0;
-        return;
-    }
-    const size_t hr = (size_t)ol * m.nrays + r;
-    const unsigned long long off = __ldg(&pv.poff[hr]);
-    const double shift0 = __ldg(&pv.shift0[hr]);
-    unsigned long long out = FILL ? rv.off[list] : 0ull; /* next record of this list */
-    uint32_t total_count = 0;
-    double prev_shift = 0.0, prev_dsm = 0.0; /* the entry before the batch's first (warp-uniform) */
-    bool have_prev = false;
-    for (uint32_t j = len; j > 0;) {
-        const uint32_t S = j < 32u ? j : 32u;
-        const int js = (int)j - 1 - (int)lane;
-        StepData sd;
-        sd.nxt = o; sd.crt = o; sd.dZ = 0.0; sd.sh_nxt = 1.0; sd.sh_crt = 1.0; sd.dsm = 0.0; sd.sqw = 0.0;
-        uint32_t ni = 0;
-        if (lane < S) {
-            sd.nxt    = __ldg(&pv.nr[off + js]);
-            sd.crt    = js ? __ldg(&pv.nr[off + js - 1]) : o;
-            sd.dZ     = __ldg(&pv.dZ[off + js]);
-            sd.sh_nxt = __ldg(&pv.shift[off + js]);
-            sd.sh_crt = js ? __ldg(&pv.shift[off + js - 1]) : shift0;
-            const double crit_nxt = __ldg(&m.lrow[(size_t)sd.nxt * m.nlines + l].criterion);
-            const double crit_crt = __ldg(&m.lrow[(size_t)sd.crt * m.nlines + l].criterion);
-            ni = n_interp_from_criteria(m, crit_crt, crit_nxt);
-            if (FILL) { sd.dsm = __ldg(&m.dshift_max[sd.nxt]); sd.sqw = __ldg(&m.sqrtw_max[sd.nxt]); }
-        }
-        uint32_t cum = ni;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, cum, d);
-            if ((int)lane >= d) cum += v;
-        }
-        const uint32_t total = __shfl_sync(0xffffffffu, cum, 31);
-        total_count += total;
-        if (FILL) {
-            const uint32_t excl = cum - ni;
-            for (uint32_t t0 = 0; t0 < total; t0 += 32) {
-                const uint32_t t = t0 + lane;
-                /* the step that owns entry t: the last lane whose exclusive prefix is <= t (prefixes are non-decreasing over lanes) */
-                int te = 0;
-#pragma unroll
-                for (int d = 16; d; d >>= 1) {
-                    const int cand = te + d;
-                    const uint32_t ex = __shfl_sync(0xffffffffu, excl, cand & 31);
-                    if (cand < 32 && ex <= t && cand < (int)S) te = cand;
-                }
-                StepData se;
-                se.nxt = __shfl_sync(0xffffffffu, sd.nxt, te); se.crt = __shfl_sync(0xffffffffu, sd.crt, te);
-                se.dZ = __shfl_sync(0xffffffffu, sd.dZ, te); se.sh_nxt = __shfl_sync(0xffffffffu, sd.sh_nxt, te);
-                se.sh_crt = __shfl_sync(0xffffffffu, sd.sh_crt, te); se.dsm = __shfl_sync(0xffffffffu, sd.dsm, te);
-                se.sqw = __shfl_sync(0xffffffffu, sd.sqw, te);
-                const uint32_t ni_e = __shfl_sync(0xffffffffu, ni, te), excl_e = __shfl_sync(0xffffffffu, excl, te);
-                const bool valid = t < total;
-                RecVals v;
-                v.shift = 0.0; v.dz = 0.0; v.iw = 0.0; v.ie = 0.0; v.io = 0.0; v.sline = 0.0; v.factor = 0.0;
-                if (valid) v = compute_record(m, l, se, ni_e - (t - excl_e), ni_e);
-                /* large-shift test of the segment (previous entry -> this entry) */
-                double pshift = __shfl_up_sync(0xffffffffu, v.shift, 1), pdsm = __shfl_up_sync(0xffffffffu, se.dsm, 1);
-                bool hp = true;
-                if (lane == 0) { pshift = prev_shift; pdsm = prev_dsm; hp = have_prev; }
-                bool large = false;
-                if (valid && hp) {
-                    const double dshift_max = (se.dsm < pdsm) ? se.dsm : pdsm;
-                    large = fabs(v.shift - pshift) > dshift_max;
-                }
-                unsigned long long word = kNoSlot;
-                const unsigned lmask = __ballot_sync(0xffffffffu, large);
-                if (lmask) {
-                    unsigned long long base = 0;
-                    if (lane == 0) base = atomicAdd(rv.lcount, (unsigned long long)__popc(lmask));
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    if (large) word = base + __popc(lmask & ((1u << lane) - 1u));
-                }
-                if (valid) {
-                    double* rp = rv.rec + (out + lane) * 8;
-                    reinterpret_cast<double2*>(rp)[0] = make_double2(v.shift, v.dz);
-                    reinterpret_cast<double2*>(rp)[1] = make_double2(v.iw, v.ie);
-                    reinterpret_cast<double2*>(rp)[2] = make_double2(v.io, se.sqw);
-                    reinterpret_cast<double2*>(rp)[3] = make_double2(v.sline, __longlong_as_double((long long)word));
-                    rv.pts[out + lane] = make_double2(v.factor, __hiloint2double((int)se.crt, (int)se.nxt));
-                }
-                const uint32_t nb = (total - t0) < 32u ? (total - t0) : 32u;
-                prev_shift = __shfl_sync(0xffffffffu, v.shift, nb - 1);
-                prev_dsm   = __shfl_sync(0xffffffffu, se.dsm, nb - 1);
-                have_prev  = true;
-                out += nb;
-            }
-        }
-        j -= S;
-    }
-    if (!FILL) {
-        if (lane == 0) cnt[list] = total_count + 1;
-        return;
-    }
-    // the origin's own entry (nr_[centre] = o, shift_[centre] = 1; solver.tpp:484-485)
-    if (lane == 0) {
-        StepData sd;
-        sd.nxt = o; sd.crt = o; sd.dZ = 0.0; sd.sh_nxt = 1.0; sd.sh_crt = 1.0;
-        sd.dsm = __ldg(&m.dshift_max[o]); sd.sqw = __ldg(&m.sqrtw_max[o]);
-        const RecVals v = compute_record(m, l, sd, 1, 1);
-        const double dshift_max = (sd.dsm < prev_dsm) ? sd.dsm : prev_dsm;
-        unsigned long long word = kNoSlot;
-        if (fabs(v.shift - prev_shift) > dshift_max) word = atomicAdd(rv.lcount, 1ull);
-        double* rp = rv.rec + out * 8;
-        reinterpret_cast<double2*>(rp)[0] = make_double2(v.shift, v.dz);
-        reinterpret_cast<double2*>(rp)[1] = make_double2(v.iw, v.ie);
-        reinterpret_cast<double2*>(rp)[2] = make_double2(v.io, sd.sqw);
-        reinterpret_cast<double2*>(rp)[3] = make_double2(v.sline, __longlong_as_double((long long)word));
-        rv.pts[out] = make_double2(v.factor, __hiloint2double((int)o, (int)o));
-    }
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -268,7 +139,10 @@ __global__ void k_off(const __grid_constant__ DevModel m, const __grid_constant_
 }
 
 // one warp per half ray; a thread owns the entries of one (step, line) element
-__global__ void __launch_bounds__(128) k_fill(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, RecView rv, DenseView dv) {
+#ifndef MGB_FILL_CTAS
+#define MGB_FILL_CTAS 5
+#endif
+__global__ void __launch_bounds__(128, MGB_FILL_CTAS) k_fill(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, RecView rv, DenseView dv) {
     const unsigned lane = threadIdx.x & 31;
     const size_t hrl = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     stage_exp_table();
@@ -326,7 +200,12 @@ __global__ void __launch_bounds__(128) k_fill(const __grid_constant__ DevModel m
                 unsigned long long b = 0;
                 if (lane == 0) b = atomicAdd(rv.lcount, (unsigned long long)__popc(lmask));
                 b = __shfl_sync(0xffffffffu, b, 0);
-                if (large) word = b + __popc(lmask & ((1u << lane) - 1u));
+                if (large) {
+                    word = b + __popc(lmask & ((1u << lane) - 1u));
+                    SlotInfo si;
+                    si.recY = out + it; si.o = o; si.lside = l | ((uint32_t)__ldg(&rv.side_of[r]) << 31);
+                    rv.slots[word] = si;
+                }
             }
             if (act) {
                 double* rp = rv.rec + (out + it) * 8;
@@ -341,33 +220,14 @@ __global__ void __launch_bounds__(128) k_fill(const __grid_constant__ DevModel m
     }
 }
 
-// slot -> (record of the segment's near entry Y, origin, line, side) for every flagged record. One warp per list.
-__global__ void __launch_bounds__(128) k_slots(const __grid_constant__ DevModel m, const __grid_constant__ PathView pv, RecView rv, const uint8_t* __restrict__ side_of,
-                                               SlotInfo* __restrict__ slots) {
-    const unsigned lane = threadIdx.x & 31;
-    const size_t list   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const size_t nlists = (size_t)rv.nob * m.nrays * m.nlines;
-    if (list >= nlists) return;
-    const uint32_t l  = (uint32_t)(list % m.nlines);
-    const size_t hrl  = list / m.nlines;
-    const uint32_t r  = (uint32_t)(hrl % m.nrays);
-    const uint32_t o  = pv.o0 + rv.ola + (uint32_t)(hrl / m.nrays);
-    const unsigned long long b = rv.off[list], e = rv.off[list + 1];
-    for (unsigned long long i = b + lane; i < e; i += 32) {
-        const unsigned long long w = (unsigned long long)__double_as_longlong(rv.rec[i * 8 + 7]);
-        if (w != kNoSlot) {
-            SlotInfo s;
-            s.recY = i; s.o = o; s.lside = l | ((uint32_t)side_of[r] << 31);
-            slots[w] = s;
-        }
-    }
-}
-
 // (dtau, S at the far end X, S at the near end Y) of every large-shift segment and bin: compute_source_dtau's line-integrated branch
 // (solver.tpp:2150-2153 -> compute_S_dtau_line_integrated :1878-2111) exactly as sweep_step of mgb_solve.cuh evaluates it.
 // trip [slot][3][nquads]. One thread per (slot, bin of the slot's line).
+#ifndef MGB_LARGE_CTAS
+#define MGB_LARGE_CTAS 8
+#endif
 template <int APPROX>
-__global__ void __launch_bounds__(128) k_large(const __grid_constant__ DevModel m, const double* __restrict__ rec, const double2* __restrict__ pts,
+__global__ void __launch_bounds__(128, MGB_LARGE_CTAS) k_large(const __grid_constant__ DevModel m, const double* __restrict__ rec, const double2* __restrict__ pts,
                                                const SlotInfo* __restrict__ slots, unsigned long long nslots, double* __restrict__ trip) {
     stage_exp_table();
     stage_erff_table();
