@@ -609,13 +609,19 @@ def run_b200_legs(args, torch, dist, cabi, synth, approx_of, rank, world, local,
     fp64_peak = ctx.fp64_peak_tflops()
     t_hbm = B / (hbm_peak * 1e9)
     t_fp64 = Fl / (fp64_peak * 1e12) if fp64_peak else 0.0
+    pinfo = ctx.pipeline_info()
+    pipeline = pinfo["kernel"] == 4
     traffic, traffic_note = None, "not captured for this configuration"
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        if world == 1 and args.npoints == 100000 and args.nside == 4 and args.nquads == 11 and n_solve_launches == int(tj.get("launches_per_step", 9)):
-            traffic, traffic_note = tj.get("k_solve_dram_bytes_per_launch"), tj.get("note", "")
+        key = "pipeline" if pipeline else "k_solve"
+        t = tj.get(key, tj if not pipeline else {})
+        if world == 1 and args.npoints == 100000 and args.nside == 4 and args.nquads == 11 and t.get("dram_bytes_per_step"):
+            traffic, traffic_note = t["dram_bytes_per_step"] / max(1, pinfo["n_ranges"] if pipeline else n_solve_launches), t.get("note", "")
     except Exception:
         pass
+    if pipeline:
+        n_solve_launches = max(1, pinfo["n_ranges"])  # one k_fill / k_large / k_sweep launch per record range
     hbm_line = {"bound": "hbm", "achieved": B / (ms_solve * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": B / (ms_solve * 1e-3) / 1e9 / hbm_peak,
                 "peak_source": peak_src, "roofline_time_ms": 1e3 * t_hbm}
     fp64_line = {"bound": "fp64", "achieved": Fl / (ms_solve * 1e-3) / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
@@ -623,7 +629,9 @@ def run_b200_legs(args, torch, dist, cabi, synth, approx_of, rank, world, local,
                  "peak_source": "mgb_measure_fp64_peak: a DFMA loop measured on this GPU in this run, 2 flop per DFMA (MEASURED_PEAKS.json holds no FP64 "
                                 "figure; nominal B200 FP64 is 37-40 TFLOP/s)", "roofline_time_ms": 1e3 * t_fp64}
     roofline = dict(fp64_line if t_fp64 >= t_hbm else hbm_line)
-    roofline.update({"kernel": "k_solve<CloseLines,false>", "traffic": traffic, "traffic_note": traffic_note,
+    kernel_name = ("solve pipeline: k_ni + k_fill (ray-entry records) -> k_large (large-shift line integrals) -> k_sweep<CloseLines> "
+                   "(eta/chi + two-sided elimination), one launch of each per record range") if pipeline else "k_solve<CloseLines,false>"
+    roofline.update({"kernel": kernel_name, "traffic": traffic, "traffic_note": traffic_note,
                      "algorithmic_bytes_per_launch": B / max(1, n_solve_launches), "algorithmic_flops_per_launch": Fl / max(1, n_solve_launches),
                      "avg_launch_ms": ms_solve / max(1, n_solve_launches), "launches_per_step": n_solve_launches,
                      "flop_model": "54*nquads*SigmaN + 110*solves (SURVEY.md 8d)",
@@ -631,6 +639,9 @@ def run_b200_legs(args, torch, dist, cabi, synth, approx_of, rank, world, local,
                      "other_bound": hbm_line if t_fp64 >= t_hbm else fp64_line,
                      "note": "roofline time = max(t_HBM, t_FP64) (SURVEY.md 8d): the FP64 pipe bounds this kernel; frac = roofline time / measured time. "
                              "N > 1: rank 0's launches"})
+    if pipeline:
+        roofline["pipeline_ms"] = {"records": pinfo["ms_records"], "line_integrals": pinfo["ms_line_integrals"], "sweep": pinfo["ms_sweep"],
+                                   "record_ranges": pinfo["n_ranges"], "note": "device time of the three stages in the last timed step (CUDA events)"}
     out = None
     if rank == 0:
         out = {"metric": "point*ray*freq Feautrier order-2 solves/s", "value": value, "unit": "solves/s", "n_gpus": world,

@@ -128,6 +128,11 @@ int mgb_run_feautrier_order_2(mgb_ctx* ctx, int approx, uint32_t o_begin, uint32
  * Parameters::min_dtau (1e-15). A half ray without a segment contributes the factor 0 to its Lambda element (the
  * reference reads an uninitialised dtau there). */
 int mgb_run_shortchar_order_0(mgb_ctx* ctx, int approx, double min_dtau, uint32_t o_begin, uint32_t o_end, mgb_stats* stats);
+/* Which kernel generation served the last run for n_off_diag = 0 (environment MGB_SOLVE_KERNEL: 1 k_solve, 2 k_solve2, 3 k_solve3,
+ * 4 = default: the streaming pipeline k_ni / k_fill -> k_large -> k_sweep of mgb_solve4.cuh; all bit-identical) and, for the
+ * pipeline, the device time of its three stages and the number of record ranges (k_sweep launches). No reference counterpart:
+ * measurement aid for bench.py. Any pointer may be NULL. */
+int mgb_solve_pipeline_info(mgb_ctx* ctx, int* kernel, float* ms_records, float* ms_line_integrals, float* ms_sweep, uint32_t* n_ranges);
 /* Copy results of the last run to the host. J: rows [o_begin,o_end) of radiation.J, (o_end-o_begin)*nfreqs.
  * Lambda (n_off_diag = 0: the diagonal operator): lambda_val [(o_end-o_begin)][nlines] holds Ls for the
  * element (p=o, k, nr=o) that Lambda::add_element accumulated (lambda.tpp:79-89), lambda_cnt the list

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("MGB_LIB") or os.path.join(_HERE, "lib", "libmagritte_
 EXPORTS = [
     "mgb_abi_version", "mgb_create", "mgb_destroy", "mgb_last_error", "mgb_set_geometry", "mgb_set_adaptive_directions", "mgb_set_thermodynamics",
     "mgb_set_lines", "mgb_set_frequencies", "mgb_set_line_state", "mgb_params_default", "mgb_set_params",
-    "mgb_run_feautrier_order_2", "mgb_run_shortchar_order_0", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
+    "mgb_run_feautrier_order_2", "mgb_run_shortchar_order_0", "mgb_solve_pipeline_info", "mgb_get_J", "mgb_get_lambda", "mgb_get_u", "mgb_lambda_capacity", "mgb_get_lambda_lists", "mgb_solve_feautrier_order_2",
     "mgb_result_ptrs_dev", "mgb_invalidate_paths", "mgb_timer_start", "mgb_timer_stop", "mgb_nccl_unique_id", "mgb_comm_init", "mgb_partition", "mgb_partition_balanced", "mgb_partition_rows",
     "mgb_allgather_results", "mgb_comm_destroy", "mgb_comm_agree", "mgb_set_radiation_field", "mgb_lp_set_parameters", "mgb_lp_set_species", "mgb_lp_add_collision_partner", "mgb_lp_set_abundance",
     "mgb_lp_set_populations", "mgb_lp_get_populations", "mgb_lp_refresh_line_state", "mgb_lp_get_line_state", "mgb_lp_compute_Jeff", "mgb_lp_get_Jeff",
@@ -223,6 +223,12 @@ class Context:
                                                        C.byref(st)), "mgb_run_feautrier_order_2")
         self.last_range = (o0, o1)
         return st
+
+    def pipeline_info(self):
+        """-> dict(kernel, ms_records, ms_line_integrals, ms_sweep, n_ranges) of the last run (mgb_solve_pipeline_info)."""
+        k, a, b, c, n = C.c_int(0), C.c_float(0), C.c_float(0), C.c_float(0), C.c_uint32(0)
+        self._check(self.lib.mgb_solve_pipeline_info(self._ctx, C.byref(k), C.byref(a), C.byref(b), C.byref(c), C.byref(n)), "mgb_solve_pipeline_info")
+        return dict(kernel=k.value, ms_records=a.value, ms_line_integrals=b.value, ms_sweep=c.value, n_ranges=n.value)
 
     def run_shortchar(self, approx=2, o_range=None, min_dtau=1.0e-15, store_u=None):
         """Solver::solve_shortchar_order_0 (solver.tpp:150-235) -> Stats; results through get_J / get_u / get_lambda_diag."""

@@ -9,7 +9,7 @@
 
 #include "mgb_ctx.h"
 #ifndef MGB_DEFAULT_SOLVE_KERNEL
-#define MGB_DEFAULT_SOLVE_KERNEL 1
+#define MGB_DEFAULT_SOLVE_KERNEL 4
 #endif
 #include "mgb_solve4.cuh"
 #include "mgb_shortchar.cuh"
@@ -599,6 +599,7 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
                 m, pv, sc, ctx->freq_chunks.as<FreqChunk>(), nchunks_f, rv, ctx->rec_trip.as<double>());
             MGB_CUDA(ctx, cudaGetLastError());
             ctx->ms_v4[2] += t3.stop();
+            ctx->ms_v4[3] += 1.f; /* record ranges (= k_sweep launches) of the run */
             launches++;
         }
         a = b;
@@ -784,7 +785,7 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
     {
         const char* v2 = getenv("MGB_SOLVE_V2");
         const char* vk = getenv("MGB_SOLVE_KERNEL"); /* 1: k_solve, 2: k_solve2, 3: k_solve3, 4: the streaming pipeline (mgb_solve4.cuh) */
-        ctx->ms_v4[0] = ctx->ms_v4[1] = ctx->ms_v4[2] = 0.f;
+        ctx->ms_v4[0] = ctx->ms_v4[1] = ctx->ms_v4[2] = ctx->ms_v4[3] = 0.f;
         ctx->solve_v2 = (vk && vk[0] >= '1' && vk[0] <= '4') ? vk[0] - '0' : ((v2 && v2[0] == '1') ? 2 : MGB_DEFAULT_SOLVE_KERNEL);
     }
     const bool lambda2 = !K && !shortchar; /* the diagonal operator: L_diag from the solve kernel, factors applied by k_reduce_lambda2 */
@@ -875,6 +876,16 @@ static int run_radiation_field(mgb_ctx* ctx, int approx, uint32_t o_begin, uint3
     st.paths_cached = all_cached ? 1 : 0;
     ctx->res_o0 = o_begin; ctx->res_o1 = o_end; ctx->res_K = K; ctx->res_valid = true; ctx->res_anis = anis;
     if (stats) *stats = st;
+    return MGB_OK;
+}
+
+extern "C" int mgb_solve_pipeline_info(mgb_ctx* ctx, int* kernel, float* ms_records, float* ms_line_integrals, float* ms_sweep, uint32_t* n_ranges) {
+    if (!ctx) return MGB_EINVAL;
+    if (kernel) *kernel = ctx->solve_v2;
+    if (ms_records) *ms_records = ctx->ms_v4[0];
+    if (ms_line_integrals) *ms_line_integrals = ctx->ms_v4[1];
+    if (ms_sweep) *ms_sweep = ctx->ms_v4[2];
+    if (n_ranges) *n_ranges = (uint32_t)ctx->ms_v4[3];
     return MGB_OK;
 }
 

@@ -90,7 +90,7 @@ struct mgb_ctx {
     double max_inverse_mass = 0.0;
     uint32_t n_freq_chunks = 0, lines_per_warp = 1; // k_solve work decomposition (build_freq_chunks)
     uint32_t n_freq_chunks2 = 0, lines_per_warp2 = 1; // k_solve2: whole lines per warp, two bins per lane
-    int solve_v2 = 1;                                 // solve kernel generation for n_off_diag = 0 (MGB_SOLVE_KERNEL = 1, 2, 3)
+    int solve_v2 = 4;                                 // solve kernel generation for n_off_diag = 0 (MGB_SOLVE_KERNEL = 1 .. 4; default 4: the pipeline)
     mgb::DevModel m{};
     // device storage
     mgb::DevBuf pos, vel, csr, nbs, dir, weight, antipod, p2b, bcond, btemp;
