@@ -502,7 +502,7 @@ template <int APPROX>
 int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, const PathChunk* ch, uint32_t nchunks_f, uint32_t& launches) {
     const DevModel& m = ctx->m;
     if (!ctx->side_ok) return ctx->fail(MGB_EUNSUPPORTED, "MGB_SOLVE_KERNEL=4 needs antipod[rr] >= nrays/2 for every rr < nrays/2");
-    static const unsigned long long budget = [] {
+    const unsigned long long budget = [] { /* read per run: tests shrink it to force many record ranges */
         const char* e = getenv("MGB_REC_BYTES");
         const unsigned long long v = e ? strtoull(e, nullptr, 10) : 0ull;
         return v ? v : (40ull << 30);

@@ -373,7 +373,10 @@ __device__ __noinline__ Lane3 step4_general(const DevModel& m, LaneLine L, Lane3
 #endif
 constexpr int kSweepWarps = MGB_SWEEP_WARPS, kSweepCtas = MGB_SWEEP_CTAS;
 
-constexpr int kRingDepth = 4;
+#ifndef MGB_SWEEP_UNROLL
+#define MGB_SWEEP_UNROLL 1
+#endif
+constexpr int kRingDepth = 4, kSweepUnroll = MGB_SWEEP_UNROLL;
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
 }
@@ -459,6 +462,7 @@ __global__ void __launch_bounds__(32 * kSweepWarps, kSweepCtas) k_sweep(const __
         }
         Trip tr; tr.dtau = tr.SX = tr.SY = 0.0;
         double shX = 0.0, dzX = 0.0;
+#pragma unroll kSweepUnroll
         for (uint32_t e = 0; e < nmax; e++) {
             const bool part = e < n;
             {

@@ -75,6 +75,40 @@ def test_bit_exact_against_twosided_oracle(ctx, name, approx):
     assert util.relerr(J, Jr) <= TOL
 
 
+@pytest.mark.parametrize("name", util.GOLDEN_CASES)
+def test_all_solve_kernel_generations_bit_identical(ctx, name, monkeypatch):
+    """MGB_SOLVE_KERNEL = 1 (k_solve), 3 (k_solve3) and 4 (the streaming pipeline of mgb_solve4.cuh, the default): J, u, Lambda and the
+    work counters must agree bit for bit, for all three ApproximationTypes; the pipeline also with a record budget so small that the
+    origins are taken in many record ranges (and the range-halving path runs)."""
+    flat, _ = util.load_golden(name)
+    ctx.set_model(flat)
+    ctx.set_params(store_intensities=1)
+    try:
+        for approx in (2, 1, 0):
+            monkeypatch.setenv("MGB_SOLVE_KERNEL", "1")
+            st1 = ctx.run(approx)
+            J1, u1 = ctx.get_J().copy(), ctx.get_u().copy()
+            l1, c1 = ctx.get_lambda()
+            assert ctx.pipeline_info()["kernel"] == 1
+            for kernel, budget in (("3", None), ("4", None), ("4", str(200 * 1024))):
+                monkeypatch.setenv("MGB_SOLVE_KERNEL", kernel)
+                if budget:
+                    monkeypatch.setenv("MGB_REC_BYTES", budget)
+                else:
+                    monkeypatch.delenv("MGB_REC_BYTES", raising=False)
+                st = ctx.run(approx)
+                info = ctx.pipeline_info()
+                assert info["kernel"] == int(kernel)
+                if budget and flat["npoints"] > 100:
+                    assert info["n_ranges"] > 3
+                l, c = ctx.get_lambda()
+                assert np.array_equal(ctx.get_J(), J1) and np.array_equal(ctx.get_u(), u1), (name, approx, kernel, budget)
+                assert np.array_equal(l, l1) and np.array_equal(c, c1)
+                assert st.n_entries == st1.n_entries and st.n_large_shift == st1.n_large_shift and st.n_solves == st1.n_solves
+    finally:
+        ctx.set_params(store_intensities=0)
+
+
 def test_chunked_run_equals_single_chunk(ctx):
     """Origin chunking (bounded scratch / path memory) must not change a single bit."""
     flat, ref = util.load_golden("wind3d_small")

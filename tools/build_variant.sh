@@ -10,6 +10,6 @@ sed -i "s#../../include/magritte_b200.h#$ROOT/include/magritte_b200.h#" "$T/mgb_
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fno-fast-math -Xptxas -v $3"
 OBJS=""
 for f in mgb_api mgb_debug mgb_comm mgb_image mgb_levelpop mgb_noalloc; do nvcc $FLAGS -c "$T/$f.cu" -o "$T/$f.o" > "$T/$f.log" 2>&1 & OBJS="$OBJS $T/$f.o"; done; wait
-grep -A2 "k_solveILi2ELb0\|k_solve3ILi2" "$T/mgb_api.log" | grep -E "Used|spill" | tr '\n' ' '; echo
+cp "$T/mgb_api.log" "$OUT/$1.ptxas.log"; grep -A2 "k_sweepILi2\|k_largeILi2\|k_fillEN" "$T/mgb_api.log" | grep -E "Used|spill" | tr '\n' ' '; echo
 nvcc -shared -o "$OUT/libmgb_$1.so" $OBJS -lcudart -ldl 2>/dev/null
 rm -rf "$T"
