@@ -181,19 +181,9 @@ __global__ void __launch_bounds__(128, MGB_FILL_CTAS) k_fill(const __grid_consta
                 have_prev = true;
             }
         }
-        const uint32_t nimax = __reduce_max_sync(0xffffffffu, ni);
-        for (uint32_t it = 0; it < nimax; it++) {
-            const bool act = it < ni;
-            RecVals v;
-            v.shift = 0.0; v.dz = 0.0; v.iw = 0.0; v.ie = 0.0; v.io = 0.0; v.sline = 0.0; v.factor = 0.0;
-            bool large = false;
-            if (act) {
-                v = compute_record(m, l, sd, ni - it, ni);
-                if (have_prev) {
-                    const double dshift_max = (sd.dsm < prev_dsm) ? sd.dsm : prev_dsm;
-                    large = fabs(v.shift - prev_shift) > dshift_max;
-                }
-            }
+        const uint32_t side_bit = (uint32_t)__ldg(&rv.side_of[r]) << 31;
+        // stores one record (and, for a flagged segment, its slot table entry); slots are handed out per warp
+        auto emit = [&](bool act, const RecVals& v, bool large, unsigned long long at, uint32_t line, uint32_t crt, uint32_t nxt, double sqw) {
             unsigned long long word = kNoSlot;
             const unsigned lmask = __ballot_sync(0xffffffffu, large);
             if (lmask) {
@@ -203,19 +193,72 @@ __global__ void __launch_bounds__(128, MGB_FILL_CTAS) k_fill(const __grid_consta
                 if (large) {
                     word = b + __popc(lmask & ((1u << lane) - 1u));
                     SlotInfo si;
-                    si.recY = out + it; si.o = o; si.lside = l | ((uint32_t)__ldg(&rv.side_of[r]) << 31);
+                    si.recY = at; si.o = o; si.lside = line | side_bit;
                     rv.slots[word] = si;
                 }
             }
             if (act) {
-                double* rp = rv.rec + (out + it) * 8;
+                double* rp = rv.rec + at * 8;
                 reinterpret_cast<double2*>(rp)[0] = make_double2(v.shift, v.dz);
                 reinterpret_cast<double2*>(rp)[1] = make_double2(v.iw, v.ie);
-                reinterpret_cast<double2*>(rp)[2] = make_double2(v.io, sd.sqw);
+                reinterpret_cast<double2*>(rp)[2] = make_double2(v.io, sqw);
                 reinterpret_cast<double2*>(rp)[3] = make_double2(v.sline, __longlong_as_double((long long)word));
-                rv.pts[out + it] = make_double2(v.factor, __hiloint2double((int)sd.crt, (int)sd.nxt));
-                prev_shift = v.shift; prev_dsm = sd.dsm; have_prev = true;
+                rv.pts[at] = make_double2(v.factor, __hiloint2double((int)crt, (int)nxt));
             }
+        };
+        // ---- the first entry of every element (sub-index i = ni: the far point of the step itself, no interpolation) ----
+        {
+            RecVals v;
+            v.shift = 0.0; v.dz = 0.0; v.iw = 0.0; v.ie = 0.0; v.io = 0.0; v.sline = 0.0; v.factor = 0.0;
+            bool large = false;
+            if (valid) {
+                v = compute_record(m, l, sd, ni, ni);
+                if (have_prev) {
+                    const double dshift_max = (sd.dsm < prev_dsm) ? sd.dsm : prev_dsm;
+                    large = fabs(v.shift - prev_shift) > dshift_max;
+                }
+            }
+            emit(valid, v, large, out, l, sd.crt, sd.nxt, sd.sqw);
+        }
+        // ---- the sub-step entries (i = ni - 1 .. 1) of all elements of the batch, compacted: lanes = entries. They are the expensive
+        //      ones (three powf interpolations each) and only some elements have them: looping per element left 8 of 32 lanes busy ----
+        const uint32_t extra = valid ? ni - 1 : 0u;
+        uint32_t incl = extra;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t x = __shfl_up_sync(0xffffffffu, incl, d);
+            if ((int)lane >= d) incl += x;
+        }
+        const uint32_t ex = incl - extra, T = __shfl_sync(0xffffffffu, incl, 31);
+        for (uint32_t q0 = 0; q0 < T; q0 += 32) {
+            const uint32_t q = q0 + lane;
+            const bool act = q < T;
+            int ow = 0; /* owner: the last lane whose exclusive prefix is <= q */
+#pragma unroll
+            for (int d = 16; d; d >>= 1) {
+                const uint32_t e2 = __shfl_sync(0xffffffffu, ex, (ow + d) & 31);
+                if (ow + d < 32 && e2 <= q) ow += d;
+            }
+            StepData so;
+            so.nxt = __shfl_sync(0xffffffffu, sd.nxt, ow); so.crt = __shfl_sync(0xffffffffu, sd.crt, ow);
+            so.dZ = __shfl_sync(0xffffffffu, sd.dZ, ow); so.sh_nxt = __shfl_sync(0xffffffffu, sd.sh_nxt, ow);
+            so.sh_crt = __shfl_sync(0xffffffffu, sd.sh_crt, ow); so.dsm = __shfl_sync(0xffffffffu, sd.dsm, ow);
+            so.sqw = __shfl_sync(0xffffffffu, sd.sqw, ow);
+            const uint32_t ni_o = __shfl_sync(0xffffffffu, ni, ow), ex_o = __shfl_sync(0xffffffffu, ex, ow), l_o = __shfl_sync(0xffffffffu, l, ow);
+            const unsigned long long out_o = __shfl_sync(0xffffffffu, out, ow);
+            RecVals v;
+            v.shift = 0.0; v.dz = 0.0; v.iw = 0.0; v.ie = 0.0; v.io = 0.0; v.sline = 0.0; v.factor = 0.0;
+            bool large = false;
+            const uint32_t it = 1 + (q - ex_o);
+            if (act) {
+                const uint32_t i = ni_o - it;
+                v = compute_record(m, l_o, so, i, ni_o);
+                /* the entry before it is sub-entry i + 1 of the same step: compute_record's shift expression for i + 1 */
+                const double dshi = (so.sh_nxt - so.sh_crt) / ni_o;
+                const double pshift = so.sh_crt + (i + 1) * dshi;
+                large = fabs(v.shift - pshift) > so.dsm; /* min(dshift_max, dshift_max) of the one point */
+            }
+            emit(act, v, large, out_o + it, l_o, so.crt, so.nxt, so.sqw);
         }
     }
 }
