@@ -84,6 +84,10 @@ __global__ void k_ecount(uint32_t nhr, uint32_t nrays, uint32_t nlines, uint32_t
     ecnt[i] = c; /* ecnt[nhr] = 0: the scan's last element is the total */
 }
 
+__device__ __forceinline__ void st_global_v4(double* p, double a, double b, double c, double d) {
+    asm volatile("st.global.v4.f64 [%0], {%1, %2, %3, %4};" ::"l"(p), "d"(a), "d"(b), "d"(c), "d"(d) : "memory");
+}
+
 struct DenseView {
     const unsigned long long* eoff; // [nhr + 1]
     uint32_t* ni;                   // [E + 1]
@@ -197,12 +201,10 @@ __global__ void __launch_bounds__(128, MGB_FILL_CTAS) k_fill(const __grid_consta
                     rv.slots[word] = si;
                 }
             }
-            if (act) {
+            if (act) { /* two 32-byte stores: whole sectors, no read-for-ownership in L2 (sm_100 256-bit vector stores) */
                 double* rp = rv.rec + at * 8;
-                reinterpret_cast<double2*>(rp)[0] = make_double2(v.shift, v.dz);
-                reinterpret_cast<double2*>(rp)[1] = make_double2(v.iw, v.ie);
-                reinterpret_cast<double2*>(rp)[2] = make_double2(v.io, sqw);
-                reinterpret_cast<double2*>(rp)[3] = make_double2(v.sline, __longlong_as_double((long long)word));
+                st_global_v4(rp, v.shift, v.dz, v.iw, v.ie);
+                st_global_v4(rp + 4, v.io, sqw, v.sline, __longlong_as_double((long long)word));
                 rv.pts[at] = make_double2(v.factor, __hiloint2double((int)crt, (int)nxt));
             }
         };
