@@ -8,6 +8,7 @@ OUT="$HERE/../lib"
 mkdir -p "$OUT"
 NVCC="${NVCC:-/usr/local/cuda/bin/nvcc}"
 FLAGS="-gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -lineinfo -fmad=false -Xcompiler -fPIC,-O2,-fno-fast-math -Xptxas -v"
+[ -n "$MGB_NO_TEST_HOOKS" ] && FLAGS="$FLAGS -DMGB_NO_TEST_HOOKS"
 pids=()
 for f in mgb_api mgb_debug mgb_comm mgb_image mgb_levelpop mgb_noalloc; do
     if [ ! -f "$OUT/$f.o" ] || [ -n "$(find "$HERE" "$HERE/../../include" -newer "$OUT/$f.o" \( -name '*.cu' -o -name '*.cuh' -o -name '*.h' \) | head -1)" ]; then

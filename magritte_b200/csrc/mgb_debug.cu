@@ -10,6 +10,7 @@ using namespace mgb;
     } while (0)
 
 namespace {
+#ifndef MGB_NO_TEST_HOOKS
 
 // One warp traces half-ray (o, r) and expands every geometric step into the sub-steps of line l
 // (l == nlines: the all-lines criterion of Solver::trace_ray / InterpHelper::get_n_interp,
@@ -93,6 +94,7 @@ __global__ void k_ddiv(unsigned long long n, const double* a, const double* b, d
     if (!(__double_as_longlong(w3) == __double_as_longlong(w1) || (w3 != w3 && w1 != w1))) out[i] = __longlong_as_double(0x4343434343434343ll);
 }
 
+#endif // MGB_NO_TEST_HOOKS
 // 8 independent DFMA chains per thread; explicit fma() because the file is compiled with -fmad=false.
 __global__ void k_dfma(double* out, int iters) {
     double a0 = threadIdx.x * 1e-9, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
@@ -108,6 +110,9 @@ __global__ void k_dfma(double* out, int iters) {
 
 extern "C" int mgb_trace_dump(mgb_ctx* ctx, uint32_t o, uint32_t rr, uint32_t l, uint32_t cap, uint32_t* nr, uint32_t* nr_interp,
                               double* interp_factor, double* shift, double* dZ, uint32_t* n_out, uint32_t* centre_out) {
+#ifdef MGB_NO_TEST_HOOKS
+    return ctx ? ctx->fail(MGB_EUNSUPPORTED, "mgb_trace_dump: this build has no test hooks (MGB_NO_TEST_HOOKS)") : MGB_EINVAL;
+#else
     if (!ctx || !nr || !nr_interp || !interp_factor || !shift || !dZ || !n_out || !centre_out) return MGB_EINVAL;
     if (!(ctx->have_geometry && ctx->have_lines && ctx->have_state)) return ctx->fail(MGB_ESTATE, "mgb_trace_dump: model incomplete");
     const DevModel& m = ctx->m;
@@ -155,9 +160,13 @@ extern "C" int mgb_trace_dump(mgb_ctx* ctx, uint32_t o, uint32_t rr, uint32_t l,
     }
     *n_out = n_tot;
     return MGB_OK;
+#endif
 }
 
 extern "C" int mgb_selftest_libm(mgb_ctx* ctx, int fn, uint64_t n, const float* x, const float* y, float* out) {
+#ifdef MGB_NO_TEST_HOOKS
+    return ctx ? ctx->fail(MGB_EUNSUPPORTED, "mgb_selftest_libm: this build has no test hooks (MGB_NO_TEST_HOOKS)") : MGB_EINVAL;
+#else
     if (!ctx || !x || !out || fn < 0 || fn > 4 || (fn == 4 && !y)) return MGB_EINVAL;
     cudaSetDevice(ctx->device);
     DevBuf dx, dy, dout;
@@ -169,6 +178,7 @@ extern "C" int mgb_selftest_libm(mgb_ctx* ctx, int fn, uint64_t n, const float* 
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     MGB_CUDA(ctx, cudaMemcpy(out, dout.p, 4 * n, cudaMemcpyDeviceToHost));
     return MGB_OK;
+#endif
 }
 
 extern "C" int mgb_measure_fp64_peak(mgb_ctx* ctx, double* tflops) {
@@ -199,6 +209,9 @@ extern "C" int mgb_measure_fp64_peak(mgb_ctx* ctx, double* tflops) {
 }
 
 extern "C" int mgb_selftest_ddiv(mgb_ctx* ctx, uint64_t n, const double* a, const double* b, double* out) {
+#ifdef MGB_NO_TEST_HOOKS
+    return ctx ? ctx->fail(MGB_EUNSUPPORTED, "mgb_selftest_ddiv: this build has no test hooks (MGB_NO_TEST_HOOKS)") : MGB_EINVAL;
+#else
     if (!ctx || !a || !b || !out) return MGB_EINVAL;
     cudaSetDevice(ctx->device);
     DevBuf da, db, dout;
@@ -210,4 +223,5 @@ extern "C" int mgb_selftest_ddiv(mgb_ctx* ctx, uint64_t n, const double* a, cons
     MGB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     MGB_CUDA(ctx, cudaMemcpy(out, dout.p, 8 * n, cudaMemcpyDeviceToHost));
     return MGB_OK;
+#endif
 }
