@@ -267,7 +267,7 @@ __global__ void __launch_bounds__(128, MGB_FILL_CTAS) k_fill(const __grid_consta
 
 // (dtau, S at the far end X, S at the near end Y) of every large-shift segment and bin: compute_source_dtau's line-integrated branch
 // (solver.tpp:2150-2153 -> compute_S_dtau_line_integrated :1878-2111) exactly as sweep_step of mgb_solve.cuh evaluates it.
-// trip [slot][3][nquads]. One thread per (slot, bin of the slot's line).
+// trip [slot][nquads][3]. One thread per (slot, bin of the slot's line).
 #ifndef MGB_LARGE_CTAS
 #define MGB_LARGE_CTAS 8
 #endif
@@ -324,8 +324,8 @@ __global__ void __launch_bounds__(128, MGB_LARGE_CTAS) k_large(const __grid_cons
         if (side == 0) S_dtau_generic<APPROX>(m, pXx, pXy, qX.x, pYx, pYy, qY.x, ll, frX, frY, dzX, dtau, S_atX, S_atY);
         else S_dtau_generic<APPROX>(m, pYx, pYy, qY.x, pXx, pXy, qX.x, ll, frY, frX, dzX, dtau, S_atY, S_atX);
     }
-    double* t = trip + slot * 3 * m.nquads + z;
-    t[0] = dtau; t[m.nquads] = S_atX; t[2 * m.nquads] = S_atY;
+    double* t = trip + (slot * m.nquads + z) * 3;
+    t[0] = dtau; t[1] = S_atX; t[2] = S_atY;
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -345,8 +345,8 @@ struct Trip { double dtau, SX, SY; };
 // The general step (first entry, boundary row, windows holding other lines, ApproximationType None): sweep_step of mgb_solve.cuh on
 // streamed records. X's record index is i - 1. Out of line, state by value.
 template <int APPROX>
-__device__ __noinline__ Lane3 step4_general(const DevModel& m, LaneLine L, Lane3 st, double freq, int side, double shX, double dzX, Rec4 y, Trip tr,
-                                            unsigned long long i, const double2* __restrict__ pts, uint32_t ll) {
+__device__ __noinline__ Lane3 step4_general(const DevModel& m, LaneLine L, Lane3 st, double freq, int side, const double* __restrict__ rec, double dzX,
+                                            Rec4 y, Trip tr, unsigned long long i, const double2* __restrict__ pts, uint32_t ll) {
     const double frY = freq * y.shift;
     double chiY, SY;
     {
@@ -385,7 +385,7 @@ __device__ __noinline__ Lane3 step4_general(const DevModel& m, LaneLine L, Lane3
             const double Bm  = 1.0 + 2.0 * inv;
             const double B   = Bm + Cb;
             const double2 qX = pts[i - 1];
-            const double Ib  = boundary_intensity(m, (uint32_t)__double2loint(qX.y), freq * shX);
+            const double Ib  = boundary_intensity(m, (uint32_t)__double2loint(qX.y), freq * rec[(i - 1) * 8]); /* X's shift */
             const double Su0 = ddiv(S0 + 2.0 * Ib * inv, B);
             st.F = 0.5 * Bm * dtau * dtau;
             st.a = Su0 * (1.0 + st.F);
@@ -501,20 +501,21 @@ __global__ void __launch_bounds__(32 * kSweepWarps, kSweepCtas) k_sweep(const __
         const uint32_t nk = __shfl_sync(0xffffffffu, n, jk > 0 ? jk : 0);
         const bool copier = kc < ch.nl;
         __syncwarp();
+        const double* src = rv.rec + bk * 8 + 2 * cc; /* this lane's 16 bytes of the next record to copy; stops at the list's last record */
+        uint32_t left = copier ? nk - 1 : 0u;          /* records after *src */
         for (int d = 0; d < kRingDepth - 1; d++) {
-            if (copier) cp_async16(&s_ring[wib][d][kc][2 * cc], rv.rec + (bk + (((uint32_t)d < nk) ? (uint32_t)d : nk - 1)) * 8 + 2 * cc);
+            if (copier) cp_async16(&s_ring[wib][d][kc][2 * cc], src);
             cp_async_commit();
+            if (left) { src += 8; left--; }
         }
         Trip tr; tr.dtau = tr.SX = tr.SY = 0.0;
         double shX = 0.0, dzX = 0.0;
 #pragma unroll kSweepUnroll
         for (uint32_t e = 0; e < nmax; e++) {
             const bool part = e < n;
-            {
-                const uint32_t ea = e + kRingDepth - 1;
-                if (copier) cp_async16(&s_ring[wib][ea % kRingDepth][kc][2 * cc], rv.rec + (bk + ((ea < nk) ? ea : nk - 1)) * 8 + 2 * cc);
-                cp_async_commit();
-            }
+            if (copier) cp_async16(&s_ring[wib][(e + kRingDepth - 1) % kRingDepth][kc][2 * cc], src);
+            cp_async_commit();
+            if (left) { src += 8; left--; }
             cp_async_wait<kRingDepth - 2>(); /* entries e and e + 1 have landed */
             __syncwarp();
             const double* yr = &s_ring[wib][e % kRingDepth][ks][0];
@@ -524,8 +525,8 @@ __global__ void __launch_bounds__(32 * kSweepWarps, kSweepCtas) k_sweep(const __
             const unsigned long long w1 = (unsigned long long)__double_as_longlong(s_ring[wib][(e + 1) % kRingDepth][ks][7]);
             Trip tn; tn.dtau = tn.SX = tn.SY = 0.0;
             if (w1 != kNoSlot && e + 1 < n) {
-                const double* tp = trip + w1 * 3 * m.nquads + z;
-                tn.dtau = __ldg(tp); tn.SX = __ldg(tp + m.nquads); tn.SY = __ldg(tp + 2 * m.nquads);
+                const double* tp = trip + (w1 * m.nquads + z) * 3;
+                tn.dtau = __ldg(tp); tn.SX = __ldg(tp + 1); tn.SY = __ldg(tp + 2);
             }
             // ---- the common step: an interior row whose window at Y holds the own line or no line ----
             const bool large = y.word != kNoSlot;
@@ -557,9 +558,9 @@ __global__ void __launch_bounds__(32 * kSweepWarps, kSweepCtas) k_sweep(const __
                     st.large_far = large;
                 }
             } else if (part) {
-                st = step4_general<APPROX>(m, L, st, freq, side, shX, dzX, y, tr, b + e, rv.pts, ll);
+                st = step4_general<APPROX>(m, L, st, freq, side, rv.rec, dzX, y, tr, b + e, rv.pts, ll);
             }
-            if (part) { shX = y.shift; dzX = y.dz; tr = tn; }
+            if (part) { dzX = y.dz; tr = tn; }
             __syncwarp(); /* the slot read here is overwritten by the next iteration's copy */
         }
         cp_async_wait<0>(); /* copies issued past the last entry must not land in the other side's ring */
