@@ -519,7 +519,7 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
         uint32_t b = a;
         unsigned long long est = 0;
         while (b < no && (b == a || est + est_bytes(b) <= budget)) { est += est_bytes(b); b++; }
-        unsigned long long nrec = 0, nelem = 0;
+        unsigned long long nrec = 0, nelem = 0, nlarge = 0;
         RecView rv{};
         DenseView dv{};
         for (;;) { /* elements and records of the range; halve the range when the records would not fit */
@@ -555,29 +555,32 @@ int run_pipeline_v4(mgb_ctx* ctx, const PathView& pv, const ScratchView& sc, con
             launches += 4;
             MGB_CUDA(ctx, cudaMemcpy(&nrec, ctx->rec_base.as<unsigned long long>() + nelem, 8, cudaMemcpyDeviceToHost));
             if (nrec * 96ull > budget + budget / 4 && b - a > 1) { b = a + (b - a) / 2; continue; }
+            const size_t nlists = (size_t)(b - a) * lists_per_o;
+            MGB_CUDA(ctx, ctx->rec_off.ensure(8 * (nlists + 1)));
+            MGB_CUDA(ctx, ctx->rec.ensure(64 * (size_t)nrec));
+            MGB_CUDA(ctx, ctx->rec_pts.ensure(16 * (size_t)nrec));
+            rv.ola = a; rv.nob = b - a; rv.off = ctx->rec_off.as<unsigned long long>(); rv.lcount = ctx->rec_lcount.as<unsigned long long>();
+            rv.rec = ctx->rec.as<double>(); rv.pts = ctx->rec_pts.as<double2>();
+            MGB_CUDA(ctx, ctx->rec_slots.ensure(sizeof(SlotInfo) * (size_t)nrec)); /* capacity: every record could end a large-shift segment */
+            rv.slots = ctx->rec_slots.as<SlotInfo>(); rv.side_of = ctx->side_of.as<uint8_t>();
+            {
+                EventTimer t1(ctx->stream);
+                t1.start();
+                MGB_CUDA(ctx, cudaMemsetAsync(ctx->rec_lcount.p, 0, 8, ctx->stream));
+                k_off<<<(unsigned)((nlists + 1 + 255) / 256), 256, 0, ctx->stream>>>(m, pv, a, b - a, dv, nelem, ctx->rec_off.as<unsigned long long>());
+                MGB_CUDA(ctx, cudaGetLastError());
+                k_fill<<<(unsigned)(((size_t)(b - a) * m.nrays * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, rv, dv);
+                MGB_CUDA(ctx, cudaGetLastError());
+                ctx->ms_v4[0] += t1.stop();
+                launches += 2;
+                MGB_CUDA(ctx, cudaMemcpy(&nlarge, ctx->rec_lcount.p, 8, cudaMemcpyDeviceToHost));
+            }
+            /* the line integrals of the flagged segments (24 * nquads bytes each) have the same budget: a range in which most segments
+               take the large-shift branch is halved and redone */
+            if (nlarge * 24ull * m.nquads > budget + budget / 4 && b - a > 1) { b = a + (b - a) / 2; continue; }
             break;
         }
         const size_t nlists = (size_t)(b - a) * lists_per_o;
-        MGB_CUDA(ctx, ctx->rec_off.ensure(8 * (nlists + 1)));
-        MGB_CUDA(ctx, ctx->rec.ensure(64 * (size_t)nrec));
-        MGB_CUDA(ctx, ctx->rec_pts.ensure(16 * (size_t)nrec));
-        rv.ola = a; rv.nob = b - a; rv.off = ctx->rec_off.as<unsigned long long>(); rv.lcount = ctx->rec_lcount.as<unsigned long long>();
-        rv.rec = ctx->rec.as<double>(); rv.pts = ctx->rec_pts.as<double2>();
-        MGB_CUDA(ctx, ctx->rec_slots.ensure(sizeof(SlotInfo) * (size_t)nrec)); /* capacity: every record could end a large-shift segment */
-        rv.slots = ctx->rec_slots.as<SlotInfo>(); rv.side_of = ctx->side_of.as<uint8_t>();
-        unsigned long long nlarge = 0;
-        {
-            EventTimer t1(ctx->stream);
-            t1.start();
-            MGB_CUDA(ctx, cudaMemsetAsync(ctx->rec_lcount.p, 0, 8, ctx->stream));
-            k_off<<<(unsigned)((nlists + 1 + 255) / 256), 256, 0, ctx->stream>>>(m, pv, a, b - a, dv, nelem, ctx->rec_off.as<unsigned long long>());
-            MGB_CUDA(ctx, cudaGetLastError());
-            k_fill<<<(unsigned)(((size_t)(b - a) * m.nrays * 32 + 127) / 128), 128, 0, ctx->stream>>>(m, pv, rv, dv);
-            MGB_CUDA(ctx, cudaGetLastError());
-            ctx->ms_v4[0] += t1.stop();
-            launches += 2;
-            MGB_CUDA(ctx, cudaMemcpy(&nlarge, ctx->rec_lcount.p, 8, cudaMemcpyDeviceToHost));
-        }
         {
             EventTimer t2(ctx->stream);
             t2.start();

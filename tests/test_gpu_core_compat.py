@@ -81,18 +81,39 @@ def test_same_script_same_level_populations(name):
 
 @pytest.mark.parametrize("name", ["wind3d_small", "wind3d_spiral_2spec"])
 def test_same_script_same_image(name):
-    spec, ref, new = both(name)
-    nu0 = float(np.array(ref.lines.line)[0])
-    dv = 20.0e3 / 2.99792458e8
-    for m in (ref, new):
-        with util.quiet():
-            m.compute_spectral_discretisation(nu0 * (1 - dv), nu0 * (1 + dv), 12)
-            assert m.compute_image_new(1, 16, 12) == 0                   # (ray_nr, Nxpix, Nypix)
-            assert m.compute_image_new(0.3, 0.5, 0.81, 16, 12) == 0      # (rx, ry, rz, Nxpix, Nypix)
-    for i in (-2, -1):
-        a, b = ref.images[i], new.images[i]
-        assert np.array_equal(np.array(a.ImX), np.array(b.ImX)) and np.array_equal(np.array(a.ImY), np.array(b.ImY))
-        assert np.array_equal(np.array(a.I), np.array(b.I))
+    """The imaging calls of the script -- compute_spectral_discretisation(nu_min, nu_max, n), compute_image_new(rx, ry, rz, Nx, Ny) and the
+    (ray_nr, Nx, Ny) overload -- through the facade, against the images the compiled reference produced for exactly these calls
+    (tests/golden/image_<name>.npz, made by make_golden_image.py with the same driver script): ImX, ImY and I bit for bit.
+    The reference is not run live here: its threaded imager segfaulted now and then inside the long-lived pytest process on the GPU box
+    (never in a process of its own, tools/image_crash_probe.py), which took the whole suite down."""
+    import os
+    from magritte_b200 import core_compat, modelbuild as mb
+    sys_path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    import importlib.util
+    mod = importlib.util.spec_from_file_location("make_golden_image", os.path.join(sys_path, "make_golden_image.py"))
+    cases = importlib.util.module_from_spec(mod)
+    mod.loader.exec_module(cases)
+    dim, li, dv, nf, dirs, (nx, ny) = cases.CASES[name]
+    g = np.load(os.path.join(sys_path, f"image_{name}.npz"))
+    spec = util.small_specs()[name]
+    with util.quiet():
+        m = mb.build(core_compat, core_compat.IoPython("mem", f"compat_img_{name}"), f"compat_img_{name}", spec)
+        mb.prepare(m)
+    if name == "wind3d_spiral_2spec":
+        m.parameters.sum_opacity_emissivity_over_all_lines = False
+    nu0 = float(np.array(m.lines.line)[li])
+    assert m.compute_spectral_discretisation(nu0 * (1 - dv / 2.99792458e8), nu0 * (1 + dv / 2.99792458e8), nf) == 0
+    for i, d in enumerate(dirs):
+        assert m.compute_image_new(float(d[0]), float(d[1]), float(d[2]), nx, ny) == 0   # (rx, ry, rz, Nxpix, Nypix)
+        im = m.images[-1]
+        assert np.array_equal(np.array(im.ImX), g[f"ImX_{i}"]) and np.array_equal(np.array(im.ImY), g[f"ImY_{i}"])
+        assert np.array_equal(np.array(im.I), g[f"I_{i}"])
+    # (ray_nr, Nxpix, Nypix): the direction of ray ray_nr (model.cpp:985-997)
+    d1 = np.array(m.geometry.rays.direction)[1]
+    assert m.compute_image_new(1, 16, 12) == 0
+    assert m.compute_image_new(float(d1[0]), float(d1[1]), float(d1[2]), 16, 12) == 0
+    a, b = m.images[-2], m.images[-1]
+    assert np.array_equal(np.array(a.ImX), np.array(b.ImX)) and np.array_equal(np.array(a.I), np.array(b.I))
 
 
 def test_container_and_parameter_behaviour():
