@@ -19,6 +19,7 @@ def both(name):
     if not refcore.available():
         pytest.skip("oracle/_ref not built")
     core_ref, _ = refcore.load()
+    core_ref.pcmt_set_n_threads_avail(8)  # as in tests/golden/make_golden*.py
     spec = util.small_specs()[name]
     out = []
     for core in (core_ref, core_compat):
