@@ -421,7 +421,10 @@ constexpr int kSweepWarps = MGB_SWEEP_WARPS, kSweepCtas = MGB_SWEEP_CTAS;
 #ifndef MGB_SWEEP_UNROLL
 #define MGB_SWEEP_UNROLL 1
 #endif
-constexpr int kRingDepth = 4, kSweepUnroll = MGB_SWEEP_UNROLL;
+#ifndef MGB_RING_DEPTH
+#define MGB_RING_DEPTH 4
+#endif
+constexpr int kRingDepth = MGB_RING_DEPTH, kSweepUnroll = MGB_SWEEP_UNROLL;
 __device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(gmem) : "memory");
 }
