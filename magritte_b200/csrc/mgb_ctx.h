@@ -131,6 +131,8 @@ struct mgb_ctx {
     double h_pos_p2b0[3] = {0, 0, 0}; // position[point2boundary[0]] when that is a valid point index
     double h_pos_last[3] = {0, 0, 0}; // position[npoints-1] (start point of a spherically symmetric image)
     mgb::DevBuf im_X, im_Y, im_len, im_start, im_shift0, im_poff, im_nr, im_nri, im_fac, im_sh, im_dz, im_I, im_nu;
+    mgb::DevBuf im_hdr, im_rec;      // imager records: per-entry headers and per-(entry, line) interpolated line data (mgb_image.cu)
+    uint32_t im_last_max = 0;        // longest pixel walk of the previous image: sizes the single-pass trace's per-pixel capacity
     // level populations on the device
     std::vector<mgb::LpSpecies*> lp;
     mgb::DevBuf lp_abundance, lp_partials, lp_flags;

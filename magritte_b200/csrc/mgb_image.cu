@@ -36,6 +36,16 @@ struct ImagePaths { // entries of every pixel of a chunk, in emission order (arr
     double* fac;
     double* sh;
     double* dz;
+    uint32_t cap; // != 0: the entries of pixel w start at w * cap (single-pass trace) instead of poff[w]
+};
+__device__ __forceinline__ unsigned long long entry_offset(const ImagePaths& ip, size_t w) {
+    return ip.cap ? (unsigned long long)w * ip.cap : ip.poff[w];
+}
+// Records of a pixel chunk: what the solve kernel reads instead of (nr, nr_interp, interp_factor) and the line table. The list of pixel
+// w starts at poff[w] + w: its start point first (position 0), then entry e at position e + 1.
+struct ImageRecs {
+    double4* hdr; // per position {shift, dZ, sqrtw_max[nr], dshift_max[nr]}
+    double4* rec; // per (position, line) {inverse_width, emissivity, opacity, S_line = emissivity / opacity}, interpolated (nr, nr_interp, factor)
 };
 
 // image.cpp:370-398
@@ -132,7 +142,9 @@ __device__ __forceinline__ uint32_t warp_n_interp_all(const DevModel& m, uint32_
 // ---------------------------------------------------------------------------------------------------
 // Tracer: one warp per pixel. reference: solver.tpp:591-607 (driver part), 808-825, 840-897, 1003-1043
 // ---------------------------------------------------------------------------------------------------
-template <bool FILL>
+// MODE 0 counts the entries, MODE 1 writes them at the pixel's scanned offset, MODE 2 does both in one pass: entries go to w * cap
+// while they fit (the host falls back to MODE 0 + 1 when some walk is longer than cap).
+template <int MODE>
 __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, unsigned long long pix0, uint32_t npix,
                                                      const double* __restrict__ ImX, const double* __restrict__ ImY,
                                                      uint32_t* __restrict__ len, uint32_t* __restrict__ start, double* __restrict__ shift0,
@@ -140,7 +152,9 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
     const unsigned lane = threadIdx.x & 31;
     const size_t w      = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     if (w >= npix) return;
-    if (FILL && len[w] == 0) return;
+    constexpr bool FILL = MODE != 0;
+    if (MODE == 1 && len[w] == 0) return;
+    const uint32_t room = MODE == 2 ? ip.cap : 0xffffffffu;
     RayFrame fr;
     surface_coords_to_3D(g, ImX[pix0 + w], ImY[pix0 + w], fr.ox, fr.oy, fr.oz);
     fr.dx = g.ray[0]; fr.dy = g.ray[1]; fr.dz = g.ray[2];
@@ -155,7 +169,7 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
     double Z = distance_origin_to_boundary(m, fr, c);
     const double sh0 = get_shift_rest(m, fr, c, Z);
     // trace_ray_imaging
-    unsigned long long off = FILL ? ip.poff[w] : 0ull;
+    const unsigned long long off = FILL ? entry_offset(ip, w) : 0ull;
     uint32_t n = 0, ns;
     bool accessed_non_boundary = false;
     double dZ = 0.0;
@@ -171,14 +185,14 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
                 if (ni > 1) {
                     const double dZ_interpl     = dZ / ni;
                     const double dshift_interpl = (shift_nxt - shift_crt) / ni;
-                    for (uint32_t i = 1 + lane; i <= ni; i += 32) {
+                    for (uint32_t i = 1 + lane; i <= ni && n + (i - 1) < room; i += 32) {
                         const unsigned long long e = off + n + (i - 1);
                         ip.nr[e] = nxt; ip.nri[e] = crt;
                         ip.sh[e]  = shift_crt + i * dshift_interpl;
                         ip.fac[e] = 1.0 - ((double)i) / ni;
                         ip.dz[e]  = dZ_interpl;
                     }
-                } else if (lane == 0) {
+                } else if (lane == 0 && n < room) {
                     const unsigned long long e = off + n;
                     ip.nr[e] = nxt; ip.nri[e] = crt; ip.sh[e] = shift_nxt; ip.fac[e] = 0.0; ip.dz[e] = dZ;
                 }
@@ -194,7 +208,7 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
             shift_nxt = get_shift_rest(m, fr, nxt, Z);
         }
     }
-    if (!FILL && lane == 0) {
+    if (MODE != 1 && lane == 0) {
         // a ray that only touched boundary points is dropped in general geometry (solver.tpp:892-896): n_tot = 1
         const uint32_t L = (accessed_non_boundary || m.spherical) ? n : 0u;
         len[w] = L; start[w] = c; shift0[w] = sh0;
@@ -253,7 +267,7 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
     if (L == 0) {
         out = TAU ? 0.0 : boundary_intensity(m, c, freq); /* n_tot = 1 (solver.tpp:616-620; :726-730) */
     } else if (TAU) {
-        const unsigned long long off = ip.poff[pix];
+        const unsigned long long off = entry_offset(ip, pix);
         Entry cur, nxt;
         cur.p1 = ip.nr[off + L - 1]; cur.p2 = ip.nri[off + L - 1]; cur.factor = ip.fac[off + L - 1]; cur.shift = ip.sh[off + L - 1];
         bool compute_curr_opacity = true;
@@ -272,7 +286,7 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
         }
         out = tau;
     } else {
-        const unsigned long long off = ip.poff[pix];
+        const unsigned long long off = entry_offset(ip, pix);
         Entry cur, nxt;
         cur.p1 = ip.nr[off + L - 1]; cur.p2 = ip.nri[off + L - 1]; cur.factor = ip.fac[off + L - 1]; cur.shift = ip.sh[off + L - 1];
         bool compute_curr_opacity = true;
@@ -321,6 +335,263 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
         double Sl = term_n + 2.0 * I_bdy_l * inverse_dtau_l;
         Sl = (Al * Su + Sl) * (1.0 + FF) * denominator;
         out = 2.0 * Sl - boundary_intensity(m, cur.p1, freq);
+    }
+    if (active) I[(size_t)pix * nfreqs + f] = out;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Records: what every frequency bin of a pixel needs from an entry does not depend on the bin -- the interpolated line data of
+// get_eta_and_chi_interpolated (solver.tpp:1259-1302: interp_linear / interp_log of the two points' inverse width, emissivity,
+// opacity), the line source function of compute_dtau_single_line (:2374-2455), sqrtw_max and dshift_max of the entry's point. The
+// generic kernel above recomputes them in each of the nfreqs lanes (two powf and a division per line and bin); here one thread per
+// entry computes them once, with the same functions in the same order, and k_image_solve_rec reads them back (warp-uniform loads).
+// ---------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k_image_records(DevModel m, uint32_t npix, const uint32_t* __restrict__ len,
+                                                       const uint32_t* __restrict__ start, const double* __restrict__ shift0, ImagePaths ip,
+                                                       ImageRecs ir) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t w      = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    stage_exp_table(); /* interp_log's powf reads it */
+    if (w >= npix) return;
+    const uint32_t L = len[w];
+    if (L == 0) return;
+    const unsigned long long off = entry_offset(ip, w), roff = ip.poff[w] + w;
+    for (uint32_t j = lane; j <= L; j += 32) {
+        Entry e;
+        double dz = 0.0;
+        if (j == 0) { /* the start point: nr_[centre], shift_[centre]; nr_interp_ / interp_factor_ value-initialised */
+            e.p1 = start[w]; e.p2 = 0u; e.factor = 0.0; e.shift = shift0[w];
+        } else {
+            const unsigned long long i = off + j - 1;
+            e.p1 = ip.nr[i]; e.p2 = ip.nri[i]; e.factor = ip.fac[i]; e.shift = ip.sh[i]; dz = ip.dz[i];
+        }
+        ir.hdr[roff + j] = make_double4(e.shift, dz, __ldg(&m.sqrtw_max[e.p1]), __ldg(&m.dshift_max[e.p1]));
+        double4* R = ir.rec + (roff + j) * m.nlines;
+        for (uint32_t l = 0; l < m.nlines; l++) {
+            const LineRow a = load_row(m, e.p1, l);
+            double iw = a.inverse_width, ie = a.emissivity, io = a.opacity, Sl = a.emissivity / a.opacity;
+            if (e.factor != 0.0) {
+                const LineRow b = load_row(m, e.p2, l);
+                iw = interp_linear(a.inverse_width, b.inverse_width, e.factor);
+                ie = interp_log(a.emissivity, b.emissivity, e.factor);
+                io = interp_log(a.opacity, b.opacity, e.factor);
+                Sl = interp_log(Sl, b.emissivity / b.opacity, e.factor);
+            }
+            R[l] = make_double4(iw, ie, io, Sl);
+        }
+    }
+}
+
+// get_eta_and_chi_interpolated<approx> (solver.tpp:1178-1202, 1259-1302) on the records of one position
+template <int APPROX>
+__device__ __forceinline__ void eta_chi_rec(const DevModel& m, const double4* __restrict__ R, double sqw, double freq, double& eta, double& chi) {
+    eta = 0.0;
+    chi = m.min_opacity;
+    if (APPROX == APPROX_NONE) {
+        for (uint32_t l = 0; l < m.nlines; l++) {
+            const double4 v   = ldg4(&R[l]);
+            const double prof = gaussian(v.x, freq - __ldg(&m.line[l]));
+            eta += prof * v.y; chi += prof * v.z;
+        }
+        return;
+    }
+    const double ub   = m.max_dist * (freq * sqw);
+    const double left = freq - ub, right = freq + ub;
+    const uint32_t lo = lower_bound_d(m.sorted_line, m.nlines, left);
+    const uint32_t hi = upper_bound_d(m.sorted_line, m.nlines, right);
+    for (uint32_t sl = lo; sl < hi; sl++) {
+        const double4 v   = ldg4(&R[__ldg(&m.sorted_map[sl])]);
+        const double prof = gaussian(v.x, freq - __ldg(&m.sorted_line[sl]));
+        eta += prof * v.y; chi += prof * v.z;
+    }
+}
+
+// compute_dtau_single_line (solver.tpp:2374-2455) on the records of the two positions
+__device__ __forceinline__ double dtau_single_line_rec(const DevModel& m, const double4 vc, const double4 vn, uint32_t l, double curr_freq,
+                                                       double next_freq, double dz, double& Sc, double& Sn) {
+    Sc = vc.w; Sn = vn.w;
+    const double linefreq = __ldg(&m.line[l]);
+    const double avg_iw   = (vc.x + vn.x) / 2.0;
+    const double curr_op = vc.z, next_op = vn.z;
+    if (curr_freq == next_freq) {
+        const double prof   = gaussian(avg_iw, curr_freq - linefreq);
+        const double avg_op = (curr_op + next_op) / 2.0;
+        return dz * (prof * avg_op + m.min_opacity);
+    }
+    const double next_pos = (linefreq - next_freq) * avg_iw;
+    const double curr_pos = (linefreq - curr_freq) * avg_iw;
+    const double diff_pos = next_pos - curr_pos;
+    const double avg_op   = (next_op + curr_op) / 2.0;
+    const float erfdiff   = erff_ool((float)next_pos) - erff_ool((float)curr_pos); /* float subtraction */
+    const double erfterm  = avg_op / diff_pos / 2.0 * (double)erfdiff;
+    return dz * (avg_iw * erfterm + m.min_opacity);
+}
+
+// compute_S_dtau_line_integrated<approx> (solver.tpp:1940-1983, 2012-2111) on the records of the two positions
+template <int APPROX>
+__device__ __forceinline__ void S_dtau_rec(const DevModel& m, const double4* __restrict__ Rc, const double4* __restrict__ Rn, double sqw_c,
+                                           double sqw_n, double currfreq, double nextfreq, double dz, double& dtau, double& Scurr,
+                                           double& Snext) {
+    double sum_dtau = 0.0, sum_c = 0.0, sum_n = 0.0;
+    if (APPROX == APPROX_NONE) {
+        for (uint32_t l = 0; l < m.nlines; l++) {
+            double Sc, Sn;
+            const double ld = dtau_single_line_rec(m, ldg4(&Rc[l]), ldg4(&Rn[l]), l, currfreq, nextfreq, dz, Sc, Sn);
+            sum_dtau += ld; sum_c += ld * Sc; sum_n += ld * Sn;
+        }
+        dtau = sum_dtau; Scurr = sum_c / sum_dtau; Snext = sum_n / sum_dtau;
+        return;
+    }
+    double left_freq, right_freq;
+    if (currfreq < nextfreq) { left_freq = currfreq; right_freq = nextfreq; }
+    else { right_freq = currfreq; left_freq = nextfreq; }
+    const double cb = m.max_dist * (right_freq * sqw_c);
+    const double nb = m.max_dist * (right_freq * sqw_n);
+    const double ub = (cb < nb) ? nb : cb;
+    const double left = left_freq - ub, right = right_freq + ub;
+    const uint32_t lo = lower_bound_d(m.sorted_line, m.nlines, left);
+    const uint32_t hi = upper_bound_d(m.sorted_line, m.nlines, right);
+    for (uint32_t sl = lo; sl < hi; sl++) {
+        double Sc, Sn;
+        const uint32_t l = __ldg(&m.sorted_map[sl]);
+        const double ld  = dtau_single_line_rec(m, ldg4(&Rc[l]), ldg4(&Rn[l]), l, currfreq, nextfreq, dz, Sc, Sn);
+        sum_dtau += ld; sum_c += ld * Sc; sum_n += ld * Sn;
+    }
+    double d = sum_dtau;
+    const double bound_min_dtau = m.min_opacity * dz;
+    if (-bound_min_dtau < d) d = (bound_min_dtau < d) ? d : bound_min_dtau;
+    dtau = d; Scurr = sum_c / d; Snext = sum_n / d;
+}
+
+// compute_source_dtau (solver.tpp:2139-2186) between the positions with headers hc (current) and hn (next)
+template <int APPROX>
+__device__ __forceinline__ void image_source_dtau_rec(const DevModel& m, const double4 hc, const double4 hn, const double4* __restrict__ Rc,
+                                                      const double4* __restrict__ Rn, double freq, bool& compute_curr_opacity, double& dtau_n,
+                                                      double& chi_c, double& chi_n, double& S_c, double& S_n) {
+    const double dshift_abs = fabs(hn.x - hc.x);
+    const double dshift_max = (hn.w < hc.w) ? hn.w : hc.w; /* std::min(curr, next) */
+    const double curr_freq = freq * hc.x, next_freq = freq * hn.x, dz = hc.y;
+    if (dshift_abs > dshift_max) {
+        compute_curr_opacity = true;
+        S_dtau_rec<APPROX>(m, Rc, Rn, hc.z, hn.z, curr_freq, next_freq, dz, dtau_n, S_c, S_n);
+    } else {
+        if (compute_curr_opacity) {
+            compute_curr_opacity = false;
+            double eta_c;
+            eta_chi_rec<APPROX>(m, Rc, hc.z, curr_freq, eta_c, chi_c);
+            S_c = ddiv(eta_c, chi_c);
+        }
+        double eta_n;
+        eta_chi_rec<APPROX>(m, Rn, hn.z, next_freq, eta_n, chi_n);
+        S_n    = ddiv(eta_n, chi_n);
+        dtau_n = 0.5 * (chi_c + chi_n) * dz;
+    }
+}
+
+// k_image_solve on the records: the same walk from the far end (position L) to the start point (position 0), the same operations.
+// Lanes = bins. A pixel takes nfreqs / 32 full warps; the nfreqs % 32 bins left over are packed with those of the next pixels into
+// one warp (100 bins: 3 full warps per pixel + one warp per 8 pixels instead of 4 warps per pixel, a fifth of them at 4 of 32 lanes).
+// Nothing in the walk is warp-collective, so lanes on different pixels simply run lists of different length.
+struct ImageItems {
+    uint32_t nfull, tail, group; // full warps per pixel, left-over bins, pixels per tail warp (0 without a tail)
+    __host__ __device__ size_t count(uint32_t npix) const { return (size_t)npix * nfull + (group ? ((size_t)npix + group - 1) / group : 0); }
+};
+#ifndef MGB_IMAGE_CTAS
+#define MGB_IMAGE_CTAS 8
+#endif
+#ifndef MGB_IMAGE_PREFETCH
+#define MGB_IMAGE_PREFETCH 1
+#endif
+template <int APPROX, bool TAU>
+__global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevModel m, uint32_t npix, uint32_t nfreqs, ImageItems it,
+                                                                         const double* __restrict__ nu, uint32_t nu_stride,
+                                                                         const uint32_t* __restrict__ len, const uint32_t* __restrict__ start,
+                                                                         ImagePaths ip, const double4* __restrict__ hdr,
+                                                                         const double4* __restrict__ rec, double* __restrict__ I) {
+    const unsigned lane = threadIdx.x & 31;
+    const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    stage_exp_table();
+    if (item >= it.count(npix)) return;
+    const size_t nfull_items = (size_t)npix * it.nfull;
+    size_t pix_l;
+    uint32_t f;
+    bool active = true;
+    if (item < nfull_items) {
+        pix_l = item / it.nfull;
+        f     = (uint32_t)(item % it.nfull) * 32 + lane;
+    } else {
+        pix_l  = (item - nfull_items) * it.group + lane / it.tail;
+        f      = it.nfull * 32 + lane % it.tail;
+        active = lane < it.group * it.tail && pix_l < npix;
+        if (!active) { pix_l = (item - nfull_items) * it.group; f = nfreqs - 1; } /* idle lanes shadow the warp's first pixel */
+    }
+    const uint32_t pix = (uint32_t)pix_l;
+    const uint32_t c   = start[pix];
+    const uint32_t L   = len[pix];
+    const double freq  = __ldg(&nu[(size_t)c * nu_stride + f]);
+    double out;
+    if (L == 0) {
+        out = TAU ? 0.0 : boundary_intensity(m, c, freq); /* n_tot = 1 (solver.tpp:616-620; :726-730) */
+    } else {
+        const unsigned long long roff = ip.poff[pix] + pix;
+        const uint32_t far_point = ip.nr[entry_offset(ip, pix) + L - 1];
+        const double4* Rc = rec + (roff + L) * m.nlines;
+        double4 hc = ldg4(&hdr[roff + L]), hn = ldg4(&hdr[roff + L - 1]);
+        bool compute_curr_opacity = true;
+        double chi_c = 0.0, chi_n = 0.0, term_c = 0.0, term_n = 0.0, dtau_n = 0.0, dtau_c, tau = 0.0;
+        double Su = 0.0, FF = 0.0, FI = 0.0;
+        for (uint32_t e = L; e-- > 0;) { /* current = position e + 1, next = position e */
+            const double4* Rn = Rc - m.nlines;
+#if MGB_IMAGE_PREFETCH
+            const double4 hnn = ldg4(&hdr[roff + (e ? e - 1 : 0)]); /* the header after next, one step ahead of its use */
+#endif
+            if (TAU) {
+                if (e != L - 1) { term_c = term_n; chi_c = chi_n; }
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                tau += dtau_n;
+            } else if (e == L - 1) {
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                const double inverse_dtau_f = drcp(dtau_n);
+                const double Cf        = 2.0 * inverse_dtau_f * inverse_dtau_f;
+                const double Bf_min_Cf = 1.0 + 2.0 * inverse_dtau_f;
+                const double Bf        = Bf_min_Cf + Cf;
+                const double I_bdy_f   = boundary_intensity(m, far_point, freq * hc.x);
+                Su = term_c + 2.0 * I_bdy_f * inverse_dtau_f;
+                Su = ddiv(Su, Bf);
+                FF = 0.5 * Bf_min_Cf * dtau_n * dtau_n;
+                FI = drcp(1.0 + FF);
+            } else {
+                term_c = term_n; dtau_c = dtau_n; chi_c = chi_n;
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                const double dtau_avg  = 0.5 * (dtau_c + dtau_n);
+                const double inverse_A = dtau_avg * dtau_c;
+                const double inverse_C = dtau_avg * dtau_n;
+                const double A         = drcp(inverse_A);
+                const double FFn       = (A * FF * FI + 1.0) * inverse_C;
+                const double FIn       = drcp(1.0 + FFn);
+                Su = (A * Su + term_c) * FIn * inverse_C;
+                FF = FFn; FI = FIn;
+            }
+#if MGB_IMAGE_PREFETCH
+            hc = hn; hn = hnn; Rc = Rn;
+#else
+            hc = hn; Rc = Rn;
+            if (e) hn = ldg4(&hdr[roff + e - 1]);
+#endif
+        }
+        if (TAU) {
+            out = tau;
+        } else { /* hc is the start point's header now */
+            const double inverse_dtau_l = drcp(dtau_n);
+            const double Al          = 2.0 * inverse_dtau_l * inverse_dtau_l;
+            const double Bl_min_Al   = 1.0 + 2.0 * inverse_dtau_l;
+            const double Bl          = Bl_min_Al + Al;
+            const double denominator = drcp(Bl * FF + Bl_min_Al);
+            const double I_bdy_l     = boundary_intensity(m, c, freq * hc.x);
+            double Sl = term_n + 2.0 * I_bdy_l * inverse_dtau_l;
+            Sl = (Al * Su + Sl) * (1.0 + FF) * denominator;
+            out = 2.0 * Sl - boundary_intensity(m, c, freq);
+        }
     }
     if (active) I[(size_t)pix * nfreqs + f] = out;
 }
@@ -451,36 +722,69 @@ static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimensio
     MGB_CUDA(ctx, ctx->im_shift0.ensure(8 * (size_t)npix)); MGB_CUDA(ctx, ctx->im_poff.ensure(8 * (size_t)npix));
     MGB_CUDA(ctx, ctx->counters.ensure(64));
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
-    // ---- count pass over the whole pixel range ----
+    // ---- pixel chunks: bounded entry storage (32 B per entry, + 32 + 32 * nlines with records) and bounded result rows ----
+    const char* env_kernel = getenv("MGB_IMAGE_KERNEL"); /* 1: the generic solve kernel, no records, two trace passes */
+    const bool generic = env_kernel && env_kernel[0] == '1';
+    const unsigned long long entry_bytes = generic ? 32ull : 64ull + 32ull * m.nlines;
+    const unsigned long long entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / entry_bytes);
+    const uint32_t pix_budget = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / (8 * (size_t)nfreqs));
+    const uint32_t nchunks_f  = (nfreqs + 31) / 32;
+    const unsigned trace_blocks = (unsigned)(((size_t)npix * 32 + 127) / 128);
+    auto ensure_entries = [&](size_t ne) -> cudaError_t {
+        cudaError_t e;
+        if ((e = ctx->im_nr.ensure(4 * ne)) != cudaSuccess || (e = ctx->im_nri.ensure(4 * ne)) != cudaSuccess ||
+            (e = ctx->im_fac.ensure(8 * ne)) != cudaSuccess || (e = ctx->im_sh.ensure(8 * ne)) != cudaSuccess ||
+            (e = ctx->im_dz.ensure(8 * ne)) != cudaSuccess) return e;
+        return cudaSuccess;
+    };
+    // ---- first pass over the whole pixel range: the entry counts -- and, when a per-pixel capacity derived from the previous image's
+    //      longest walk (512 the first time) fits the budget, the entries themselves at pixel * cap (one trace instead of two) ----
+    uint32_t cap = 0;
+    if (!generic && npix <= pix_budget) {
+        uint32_t want = ctx->im_last_max ? std::max<uint32_t>(128u, (ctx->im_last_max + ctx->im_last_max / 4 + 31u) & ~31u) : 512u;
+        if (const char* v = getenv("MGB_IMAGE_CAP")) want = (uint32_t)std::max(1l, atol(v)); /* tests: force the fallback */
+        if ((unsigned long long)want * npix <= entry_budget) cap = want;
+    }
     Stopwatch tt(ctx->stream);
     tt.start();
-    ImagePaths none{};
-    k_image_trace<false><<<(unsigned)(((size_t)npix * 32 + 127) / 128), 128, 0, ctx->stream>>>(
-        m, g, pix_begin, npix, ctx->im_X.as<double>(), ctx->im_Y.as<double>(), ctx->im_len.as<uint32_t>(), ctx->im_start.as<uint32_t>(),
-        ctx->im_shift0.as<double>(), none, ctx->counters.as<unsigned long long>());
+    if (cap) {
+        MGB_CUDA(ctx, ensure_entries((size_t)cap * npix));
+        ImagePaths capped{nullptr, ctx->im_nr.as<uint32_t>(), ctx->im_nri.as<uint32_t>(), ctx->im_fac.as<double>(), ctx->im_sh.as<double>(),
+                          ctx->im_dz.as<double>(), cap};
+        k_image_trace<2><<<trace_blocks, 128, 0, ctx->stream>>>(m, g, pix_begin, npix, ctx->im_X.as<double>(), ctx->im_Y.as<double>(),
+                                                                 ctx->im_len.as<uint32_t>(), ctx->im_start.as<uint32_t>(),
+                                                                 ctx->im_shift0.as<double>(), capped, ctx->counters.as<unsigned long long>());
+    } else {
+        ImagePaths none{};
+        k_image_trace<0><<<trace_blocks, 128, 0, ctx->stream>>>(m, g, pix_begin, npix, ctx->im_X.as<double>(), ctx->im_Y.as<double>(),
+                                                                 ctx->im_len.as<uint32_t>(), ctx->im_start.as<uint32_t>(),
+                                                                 ctx->im_shift0.as<double>(), none, ctx->counters.as<unsigned long long>());
+    }
     MGB_CUDA(ctx, cudaGetLastError());
     st.n_launches++;
     st.ms_trace += tt.stop();
-    std::vector<uint32_t> hlen(npix);
     unsigned long long cnt[2];
-    MGB_CUDA(ctx, cudaMemcpy(hlen.data(), ctx->im_len.p, 4 * (size_t)npix, cudaMemcpyDeviceToHost));
     MGB_CUDA(ctx, cudaMemcpy(cnt, ctx->counters.p, 16, cudaMemcpyDeviceToHost));
     st.n_entries = cnt[0]; st.max_ray_length = (uint32_t)cnt[1];
-    // ---- pixel chunks: bounded entry storage (32 B per entry) and bounded result rows ----
-    const unsigned long long entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / 32ull);
-    const uint32_t pix_budget = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / (8 * (size_t)nfreqs));
-    const uint32_t nchunks_f  = (nfreqs + 31) / 32;
+    ctx->im_last_max = (uint32_t)cnt[1];
+    if (cap && (cnt[1] > cap || cnt[0] + npix > entry_budget)) cap = 0; /* some walk did not fit: count is known, fill in a second pass */
+    std::vector<uint32_t> hlen;
+    if (!cap) {
+        hlen.resize(npix);
+        MGB_CUDA(ctx, cudaMemcpy(hlen.data(), ctx->im_len.p, 4 * (size_t)npix, cudaMemcpyDeviceToHost));
+    }
     for (uint32_t p0 = 0; p0 < npix;) {
         uint32_t p1 = p0;
         unsigned long long ents = 0;
-        while (p1 < npix && (p1 - p0) < pix_budget) {
-            if (p1 > p0 && ents + hlen[p1] > entry_budget) break;
-            ents += hlen[p1]; p1++;
-        }
+        if (cap) { p1 = npix; ents = cnt[0]; }
+        else
+            while (p1 < npix && (p1 - p0) < pix_budget) {
+                if (p1 > p0 && ents + hlen[p1] + (p1 - p0) > entry_budget) break;
+                ents += hlen[p1]; p1++;
+            }
         const uint32_t np = p1 - p0;
         const size_t ne   = (size_t)std::max<unsigned long long>(ents, 1);
-        MGB_CUDA(ctx, ctx->im_nr.ensure(4 * ne)); MGB_CUDA(ctx, ctx->im_nri.ensure(4 * ne)); MGB_CUDA(ctx, ctx->im_fac.ensure(8 * ne));
-        MGB_CUDA(ctx, ctx->im_sh.ensure(8 * ne)); MGB_CUDA(ctx, ctx->im_dz.ensure(8 * ne));
+        if (!cap) MGB_CUDA(ctx, ensure_entries(ne));
         MGB_CUDA(ctx, ctx->im_I.ensure(8 * (size_t)np * nfreqs));
         tt.start();
         const uint32_t* len_c = ctx->im_len.as<uint32_t>() + p0;
@@ -489,25 +793,47 @@ static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimensio
         cub::DeviceScan::ExclusiveSum(nullptr, tmp, len_c, poff, (int64_t)np, ctx->stream);
         MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
         MGB_CUDA(ctx, cub::DeviceScan::ExclusiveSum(ctx->cub_tmp.p, tmp, len_c, poff, (int64_t)np, ctx->stream));
+        st.n_launches++;
         ImagePaths ip{poff, ctx->im_nr.as<uint32_t>(), ctx->im_nri.as<uint32_t>(), ctx->im_fac.as<double>(), ctx->im_sh.as<double>(),
-                      ctx->im_dz.as<double>()};
-        k_image_trace<true><<<(unsigned)(((size_t)np * 32 + 127) / 128), 128, 0, ctx->stream>>>(
-            m, g, pix_begin + p0, np, ctx->im_X.as<double>(), ctx->im_Y.as<double>(), ctx->im_len.as<uint32_t>() + p0,
-            ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip, nullptr);
-        MGB_CUDA(ctx, cudaGetLastError());
-        st.n_launches += 2;
+                      ctx->im_dz.as<double>(), cap};
+        if (!cap) {
+            k_image_trace<1><<<(unsigned)(((size_t)np * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+                m, g, pix_begin + p0, np, ctx->im_X.as<double>(), ctx->im_Y.as<double>(), ctx->im_len.as<uint32_t>() + p0,
+                ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip, nullptr);
+            MGB_CUDA(ctx, cudaGetLastError());
+            st.n_launches++;
+        }
         st.ms_trace += tt.stop();
         tt.start();
         const size_t nitems = (size_t)np * nchunks_f;
         const unsigned blocks = (unsigned)((nitems * 32 + 127) / 128);
         const uint32_t stride = nu_per_point ? nfreqs : 0u;
+        if (generic) {
 #define MGB_IMAGE_LAUNCH(A, T)                                                                                                          \
     k_image_solve<A, T><<<blocks, 128, 0, ctx->stream>>>(m, np, nfreqs, nchunks_f, ctx->im_nu.as<double>(), stride, len_c,              \
                                                          ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip,         \
                                                          ctx->im_I.as<double>())
-        if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
-        else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
+            if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
+            else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
 #undef MGB_IMAGE_LAUNCH
+        } else {
+            const size_t npos = ne + np; /* every pixel's entries + its start point */
+            MGB_CUDA(ctx, ctx->im_hdr.ensure(32 * npos));
+            MGB_CUDA(ctx, ctx->im_rec.ensure(32 * npos * m.nlines));
+            ImageRecs ir{ctx->im_hdr.as<double4>(), ctx->im_rec.as<double4>()};
+            k_image_records<<<(unsigned)(((size_t)np * 32 + 127) / 128), 128, 0, ctx->stream>>>(
+                m, np, len_c, ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip, ir);
+            MGB_CUDA(ctx, cudaGetLastError());
+            st.n_launches++;
+            ImageItems it{nfreqs / 32, nfreqs % 32, (nfreqs % 32) ? 32 / (nfreqs % 32) : 0};
+            const unsigned rblocks = (unsigned)((it.count(np) * 32 + 127) / 128);
+#define MGB_IMAGE_LAUNCH(A, T)                                                                                                          \
+    k_image_solve_rec<A, T><<<rblocks, 128, 0, ctx->stream>>>(m, np, nfreqs, it, ctx->im_nu.as<double>(), stride, len_c,                \
+                                                              ctx->im_start.as<uint32_t>() + p0, ip, ir.hdr, ir.rec, ctx->im_I.as<double>())
+            if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
+            else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
+#undef MGB_IMAGE_LAUNCH
+        }
         MGB_CUDA(ctx, cudaGetLastError());
         st.n_launches++;
         st.ms_solve += tt.stop();

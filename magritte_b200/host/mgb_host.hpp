@@ -978,9 +978,9 @@ class Model {
         const double dir[3] = {rx, ry, rz};
         const bool per_point = spectralDiscretisation == SD_Lines;
         im.freqs = per_point ? std::vector<double>() : image_nu;
-        std::vector<double> ptot((size_t)nlspecs() * npoints);
-        for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
         if (state_uploaded != state_serial) { /* the imager reads the line state: upload it only when the host arrays changed since the last upload */
+            std::vector<double> ptot((size_t)nlspecs() * npoints);
+            for (Size l = 0; l < nlspecs(); l++) std::copy(lineProducingSpecies[l].population_tot.begin(), lineProducingSpecies[l].population_tot.end(), ptot.begin() + (size_t)l * npoints);
             check(mgb_set_line_state(ctx, emissivity.data(), opacity.data(), inverse_width.data(), ptot.data()), "mgb_set_line_state");
             state_uploaded = state_serial;
         }

@@ -68,3 +68,27 @@ def test_image_options_and_errors(ctx):
     for args in [(1, 3, d), (2, 3, (0.0, 0.0, 0.0)), (2, 1, (1.0, 0.0, 0.0)), (2, 2, d)]:
         with pytest.raises(cabi.MgbError):
             ctx.image(args[0], args[1], args[2], nx, ny, flat["nu_image"])
+
+
+@pytest.mark.parametrize("name", ["velgrad_1d", "wind3d_spiral_2spec"])
+def test_image_kernels_bit_identical(ctx, name, monkeypatch):
+    """The record path (single-pass trace + k_image_records + k_image_solve_rec, the default), its fallback when a walk does not
+    fit the per-pixel capacity, and the generic kernel (MGB_IMAGE_KERNEL=1) give the same bits, intensities and optical depths."""
+    from magritte_b200.flatten import approx_of
+    flat, img = util.load_golden_image(name)
+    ctx.set_model(flat, frequencies=False)
+    approx = approx_of(flat["params"])
+    d = img["directions"][-1]
+    for tau in (False, True):
+        monkeypatch.delenv("MGB_IMAGE_KERNEL", raising=False)
+        monkeypatch.delenv("MGB_IMAGE_CAP", raising=False)
+        _, _, I0, st0 = ctx.image(approx, img["dimension"], d, img["nx"], img["ny"], flat["nu_image"], optical_depth=tau)
+        monkeypatch.setenv("MGB_IMAGE_CAP", "3")
+        _, _, I1, st1 = ctx.image(approx, img["dimension"], d, img["nx"], img["ny"], flat["nu_image"], optical_depth=tau)
+        monkeypatch.delenv("MGB_IMAGE_CAP")
+        monkeypatch.setenv("MGB_IMAGE_KERNEL", "1")
+        _, _, I2, st2 = ctx.image(approx, img["dimension"], d, img["nx"], img["ny"], flat["nu_image"], optical_depth=tau)
+        assert np.array_equal(I0, I1) and np.array_equal(I0, I2)
+        assert st0.n_entries == st1.n_entries == st2.n_entries and st0.max_ray_length == st2.max_ray_length
+        if st0.max_ray_length > 3:
+            assert st1.n_launches == st0.n_launches + 1  # the second trace pass
