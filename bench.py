@@ -678,14 +678,17 @@ def run_b200_legs(args, torch, dist, cabi, synth, approx_of, rank, world, local,
         sync()
         ctx.timer_start()
         t0 = time.perf_counter()
+        img_each = []
         for d in [(1.0, 0.0, 0.0), (0.3, 0.5, 0.81)]:
+            t1 = time.perf_counter()
             _, _, I_img, ist = ctx.image(2, 3, d, nx, ny, nu_img, pix_range=(p0, p1))
+            img_each.append({"wall_ms": (time.perf_counter() - t1) * 1e3, "call_ms": ist.ms_total, "trace": ist.ms_trace, "solve": ist.ms_solve})
         ms_img = max(ctx.timer_stop(), (time.perf_counter() - t0) * 1e3)
         ms_img = max_over_ranks(ms_img) / 2
         if out is not None:
             out["image"] = {"metric": "pixel*freq image solves/s (Solver::image_feautrier_order_2_new_imager)", "value": npix * args.image_freqs / (ms_img * 1e-3),
                             "unit": "solves/s", "ms_per_image": ms_img, "pixels": [nx, ny], "nfreqs": args.image_freqs,
-                            "kernel_ms": {"trace": ist.ms_trace, "solve": ist.ms_solve}, "entries_per_pixel": ist.n_entries / max(1, ist.n_pixels),
+                            "kernel_ms": {"trace": ist.ms_trace, "solve": ist.ms_solve}, "each": img_each, "entries_per_pixel": ist.n_entries / max(1, ist.n_pixels),
                             "note": "end to end through mgb_image_feautrier_order_2 with host buffers (D2H of the image inside the timed region); "
                                     f"the {flat['npoints']}-point model of this bench (configs[4]'s 10M-point cloud: image_10m); pixels/{world} per rank"}
     ctx.close()

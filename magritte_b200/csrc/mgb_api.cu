@@ -256,6 +256,7 @@ extern "C" int mgb_set_lines(mgb_ctx* ctx, uint32_t nlspecs, const uint32_t* nra
     MGB_TRY(upload(ctx, ctx->line, line, 8 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->line_A, einstein_A, 8 * (size_t)nlines));
     MGB_TRY(upload(ctx, ctx->sorted_line, sline.data(), 8 * (size_t)nlines));
+    ctx->h_sorted_line = sline; /* the imager selects the lines an image can reach on the host */
     MGB_TRY(upload(ctx, ctx->sorted_map, smap.data(), 4 * (size_t)nlines));
     std::vector<uint32_t> spos(nlines);
     for (uint32_t i = 0; i < nlines; i++) spos[smap[i]] = i;

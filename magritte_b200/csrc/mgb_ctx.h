@@ -132,7 +132,26 @@ struct mgb_ctx {
     double h_pos_last[3] = {0, 0, 0}; // position[npoints-1] (start point of a spherically symmetric image)
     mgb::DevBuf im_X, im_Y, im_len, im_start, im_shift0, im_poff, im_nr, im_nri, im_fac, im_sh, im_dz, im_I, im_nu;
     mgb::DevBuf im_hdr, im_rec;      // imager records: per-entry headers and per-(entry, line) interpolated line data (mgb_image.cu)
+    std::vector<double> h_sorted_line; // host copy of lines.sorted_line
     uint32_t im_last_max = 0;        // longest pixel walk of the previous image: sizes the single-pass trace's per-pixel capacity
+    // imager result path: slices of the image go device -> this pinned staging buffer on a second stream while the next slice is
+    // solved; host threads move them on into the caller's (pageable) buffer
+    struct PinnedBuf {
+        void* p = nullptr; size_t bytes = 0;
+        ~PinnedBuf() { if (p) cudaFreeHost(p); }
+        cudaError_t ensure(size_t n) {
+            if (n <= bytes && p) return cudaSuccess;
+            if (p) cudaFreeHost(p);
+            p = nullptr; bytes = 0;
+            cudaError_t e = cudaHostAlloc(&p, n, cudaHostAllocDefault);
+            if (e == cudaSuccess) bytes = n; else p = nullptr;
+            return e;
+        }
+    } im_stage;
+    struct OwnedStream {
+        cudaStream_t s = nullptr;
+        ~OwnedStream() { if (s) cudaStreamDestroy(s); }
+    } im_copy_stream;
     // level populations on the device
     std::vector<mgb::LpSpecies*> lp;
     mgb::DevBuf lp_abundance, lp_partials, lp_flags;

@@ -2,18 +2,31 @@
 //
 //   host      Image::set_coordinates_projection_surface (image.cpp:221-368), Geometry::get_closest_bdy_point_in_custom_raydir
 //             (geometry.tpp:346-364): a loop over the boundary points, done once per call on the host copies kept by mgb_set_geometry
-//   k_image_trace<FILL>   one warp per pixel: pixel -> 3D origin (image.cpp:370-398), walk over boundary neighbours to the boundary
+//   k_image_trace<MODE>   one warp per pixel: pixel -> 3D origin (image.cpp:370-398), walk over boundary neighbours to the boundary
 //             point closest to the ray (trace_ray_imaging_get_start, solver.tpp:808-825), Rest-frame imaging trace with the
 //             all-lines sub-stepping of set_data (trace_ray_imaging :840-897, set_data :1003-1043, InterpHelper::get_n_interp).
-//             FILL = false counts the entries, FILL = true writes them (nr, nr_interp, interp_factor, shift, dZ) at the pixel's offset.
-//   k_image_solve<APPROX> one warp per (pixel, 32 frequency bins), lanes = bins: image_feautrier_order_2 (:2462-2574), i.e. the
-//             reference's forward elimination from the far end of the ray to the start point, in the reference's own operation
-//             order (no re-ordering here: Image.I is bit-identical to the CPU reference).
+//             MODE 2 (the usual case) counts AND writes the entries (nr, nr_interp, interp_factor, shift, dZ) in one pass, at
+//             pixel * cap with cap taken from the previous image's longest walk; when a walk does not fit (or the budget is small)
+//             MODE 0 counts and MODE 1 writes at the scanned offsets (two passes). 40 registers, 48 warps per SM: a pointer chase.
+//   k_image_records       one thread per entry: everything the bins of a pixel share (interpolated line data of every line, line
+//             source function, sqrtw_max / dshift_max of the entry's point), computed once instead of once per bin
+//   k_image_solve_rec<APPROX, TAU>  lanes = bins (3 full warps per pixel for 100 bins, the 4 left-over bins of 8 pixels share one
+//             warp): image_feautrier_order_2 (:2462-2574), i.e. the reference's forward elimination from the far end of the ray to
+//             the start point, in the reference's own operation order (no re-ordering: Image.I is bit-identical to the CPU
+//             reference). Launched per slice of pixels; a finished slice goes to pinned staging on a second stream while the next is
+//             solved, host threads move it on into the caller's buffer.
+//   k_image_solve<APPROX, TAU>      the first version of the solve (MGB_IMAGE_KERNEL=1): no records, every lane calls the generic
+//             eta_chi_interp / S_dtau_line_integrated of mgb_device.cuh on (nr, nr_interp, factor). Kept as the in-tree cross-check
+//             (tests/test_gpu_image.py::test_image_kernels_bit_identical).
 // Frequencies of an image are not tied to the lines (compute_spectral_discretisation(nu_min, nu_max, n)), so eta/chi use the
-// generic window search of mgb_device.cuh (eta_chi_interp / S_dtau_line_integrated), exactly the reference's loops.
+// generic window search (lower / upper bound on the sorted line frequencies), exactly the reference's loops.
 #include <algorithm>
 #include <cmath>
+#include <cstring>
+#include <thread>
+#include <vector>
 
+#include <cub/device/device_reduce.cuh>
 #include <cub/device/device_scan.cuh>
 
 #include "mgb_ctx.h"
@@ -45,7 +58,11 @@ __device__ __forceinline__ unsigned long long entry_offset(const ImagePaths& ip,
 // w starts at poff[w] + w: its start point first (position 0), then entry e at position e + 1.
 struct ImageRecs {
     double4* hdr; // per position {shift, dZ, sqrtw_max[nr], dshift_max[nr]}
-    double4* rec; // per (position, line) {inverse_width, emissivity, opacity, S_line = emissivity / opacity}, interpolated (nr, nr_interp, factor)
+    double4* rec; // per (position, line slot) {inverse_width, emissivity, opacity, S_line = emissivity / opacity}, interpolated (nr, nr_interp, factor)
+    // CloseLines: the slots are the sorted line indices [slo, slo + nsel) that some bin of this image can have in its window (bounds of
+    // frequency x shift over all pixels, widened by the largest window); ApproximationType None sums every line: slo = 0, nsel = nlines,
+    // natural line order
+    uint32_t slo, nsel;
 };
 
 // image.cpp:370-398
@@ -144,8 +161,11 @@ __device__ __forceinline__ uint32_t warp_n_interp_all(const DevModel& m, uint32_
 // ---------------------------------------------------------------------------------------------------
 // MODE 0 counts the entries, MODE 1 writes them at the pixel's scanned offset, MODE 2 does both in one pass: entries go to w * cap
 // while they fit (the host falls back to MODE 0 + 1 when some walk is longer than cap).
+#ifndef MGB_TRACE_CTAS
+#define MGB_TRACE_CTAS 12
+#endif
 template <int MODE>
-__global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, unsigned long long pix0, uint32_t npix,
+__global__ void __launch_bounds__(128, MGB_TRACE_CTAS) k_image_trace(DevModel m, ImageGeom g, unsigned long long pix0, uint32_t npix,
                                                      const double* __restrict__ ImX, const double* __restrict__ ImY,
                                                      uint32_t* __restrict__ len, uint32_t* __restrict__ start, double* __restrict__ shift0,
                                                      ImagePaths ip, unsigned long long* __restrict__ counters) {
@@ -168,6 +188,7 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
     }
     double Z = distance_origin_to_boundary(m, fr, c);
     const double sh0 = get_shift_rest(m, fr, c, Z);
+    double sh_min = sh0, sh_max = sh0; /* bounds of the shifts along this pixel's ray (the sub-steps interpolate between them) */
     // trace_ray_imaging
     const unsigned long long off = FILL ? entry_offset(ip, w) : 0ull;
     uint32_t n = 0, ns;
@@ -178,7 +199,9 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
     if (nxt < m.npoints) {
         double shift_crt = get_shift_rest(m, fr, crt, Z - dZ);
         double shift_nxt = get_shift_rest(m, fr, nxt, Z);
+        sh_min = fmin(sh_min, shift_crt); sh_max = fmax(sh_max, shift_crt);
         for (;;) {
+            sh_min = fmin(sh_min, shift_nxt); sh_max = fmax(sh_max, shift_nxt);
             // set_data (solver.tpp:1003-1043)
             const uint32_t ni = warp_n_interp_all(m, crt, nxt, lane);
             if (FILL) {
@@ -214,6 +237,13 @@ __global__ void __launch_bounds__(128) k_image_trace(DevModel m, ImageGeom g, un
         len[w] = L; start[w] = c; shift0[w] = sh0;
         atomicAdd(&counters[0], (unsigned long long)L);
         atomicMax((unsigned int*)&counters[1], n); /* get_ray_lengths_max_new_imager counts every walk */
+        /* positive doubles order like their bit patterns; a non-positive or NaN shift makes the host keep every line */
+        if (sh_min > 0.0 && sh_max < CUDART_INF) {
+            atomicMin(&counters[2], (unsigned long long)__double_as_longlong(sh_min));
+            atomicMax(&counters[3], (unsigned long long)__double_as_longlong(sh_max));
+        } else {
+            atomicMin(&counters[2], 0ull);
+        }
     }
 }
 
@@ -346,6 +376,7 @@ __global__ void __launch_bounds__(128) k_image_solve(DevModel m, uint32_t npix, 
 // generic kernel above recomputes them in each of the nfreqs lanes (two powf and a division per line and bin); here one thread per
 // entry computes them once, with the same functions in the same order, and k_image_solve_rec reads them back (warp-uniform loads).
 // ---------------------------------------------------------------------------------------------------
+template <bool CLOSE>
 __global__ void __launch_bounds__(128) k_image_records(DevModel m, uint32_t npix, const uint32_t* __restrict__ len,
                                                        const uint32_t* __restrict__ start, const double* __restrict__ shift0, ImagePaths ip,
                                                        ImageRecs ir) {
@@ -366,8 +397,9 @@ __global__ void __launch_bounds__(128) k_image_records(DevModel m, uint32_t npix
             e.p1 = ip.nr[i]; e.p2 = ip.nri[i]; e.factor = ip.fac[i]; e.shift = ip.sh[i]; dz = ip.dz[i];
         }
         ir.hdr[roff + j] = make_double4(e.shift, dz, __ldg(&m.sqrtw_max[e.p1]), __ldg(&m.dshift_max[e.p1]));
-        double4* R = ir.rec + (roff + j) * m.nlines;
-        for (uint32_t l = 0; l < m.nlines; l++) {
+        double4* R = ir.rec + (roff + j) * ir.nsel;
+        for (uint32_t k = 0; k < ir.nsel; k++) {
+            const uint32_t l = CLOSE ? __ldg(&m.sorted_map[ir.slo + k]) : k;
             const LineRow a = load_row(m, e.p1, l);
             double iw = a.inverse_width, ie = a.emissivity, io = a.opacity, Sl = a.emissivity / a.opacity;
             if (e.factor != 0.0) {
@@ -377,14 +409,14 @@ __global__ void __launch_bounds__(128) k_image_records(DevModel m, uint32_t npix
                 io = interp_log(a.opacity, b.opacity, e.factor);
                 Sl = interp_log(Sl, b.emissivity / b.opacity, e.factor);
             }
-            R[l] = make_double4(iw, ie, io, Sl);
+            R[k] = make_double4(iw, ie, io, Sl);
         }
     }
 }
 
 // get_eta_and_chi_interpolated<approx> (solver.tpp:1178-1202, 1259-1302) on the records of one position
 template <int APPROX>
-__device__ __forceinline__ void eta_chi_rec(const DevModel& m, const double4* __restrict__ R, double sqw, double freq, double& eta, double& chi) {
+__device__ __forceinline__ void eta_chi_rec(const DevModel& m, const double4* __restrict__ R, uint32_t slo, uint32_t nsel, double sqw, double freq, double& eta, double& chi) {
     eta = 0.0;
     chi = m.min_opacity;
     if (APPROX == APPROX_NONE) {
@@ -397,20 +429,20 @@ __device__ __forceinline__ void eta_chi_rec(const DevModel& m, const double4* __
     }
     const double ub   = m.max_dist * (freq * sqw);
     const double left = freq - ub, right = freq + ub;
-    const uint32_t lo = lower_bound_d(m.sorted_line, m.nlines, left);
-    const uint32_t hi = upper_bound_d(m.sorted_line, m.nlines, right);
+    /* every line a bin of this image can reach is in [slo, slo + nsel): the search over that range finds the full search's bounds */
+    const uint32_t lo = slo + lower_bound_d(m.sorted_line + slo, nsel, left);
+    const uint32_t hi = slo + upper_bound_d(m.sorted_line + slo, nsel, right);
     for (uint32_t sl = lo; sl < hi; sl++) {
-        const double4 v   = ldg4(&R[__ldg(&m.sorted_map[sl])]);
+        const double4 v   = ldg4(&R[sl - slo]); /* the records are in sorted-line order from slo on */
         const double prof = gaussian(v.x, freq - __ldg(&m.sorted_line[sl]));
         eta += prof * v.y; chi += prof * v.z;
     }
 }
 
 // compute_dtau_single_line (solver.tpp:2374-2455) on the records of the two positions
-__device__ __forceinline__ double dtau_single_line_rec(const DevModel& m, const double4 vc, const double4 vn, uint32_t l, double curr_freq,
+__device__ __forceinline__ double dtau_single_line_rec(const DevModel& m, const double4 vc, const double4 vn, double linefreq, double curr_freq,
                                                        double next_freq, double dz, double& Sc, double& Sn) {
     Sc = vc.w; Sn = vn.w;
-    const double linefreq = __ldg(&m.line[l]);
     const double avg_iw   = (vc.x + vn.x) / 2.0;
     const double curr_op = vc.z, next_op = vn.z;
     if (curr_freq == next_freq) {
@@ -429,14 +461,14 @@ __device__ __forceinline__ double dtau_single_line_rec(const DevModel& m, const 
 
 // compute_S_dtau_line_integrated<approx> (solver.tpp:1940-1983, 2012-2111) on the records of the two positions
 template <int APPROX>
-__device__ __forceinline__ void S_dtau_rec(const DevModel& m, const double4* __restrict__ Rc, const double4* __restrict__ Rn, double sqw_c,
+__device__ __forceinline__ void S_dtau_rec(const DevModel& m, const double4* __restrict__ Rc, const double4* __restrict__ Rn, uint32_t slo, uint32_t nsel, double sqw_c,
                                            double sqw_n, double currfreq, double nextfreq, double dz, double& dtau, double& Scurr,
                                            double& Snext) {
     double sum_dtau = 0.0, sum_c = 0.0, sum_n = 0.0;
     if (APPROX == APPROX_NONE) {
         for (uint32_t l = 0; l < m.nlines; l++) {
             double Sc, Sn;
-            const double ld = dtau_single_line_rec(m, ldg4(&Rc[l]), ldg4(&Rn[l]), l, currfreq, nextfreq, dz, Sc, Sn);
+            const double ld = dtau_single_line_rec(m, ldg4(&Rc[l]), ldg4(&Rn[l]), __ldg(&m.line[l]), currfreq, nextfreq, dz, Sc, Sn);
             sum_dtau += ld; sum_c += ld * Sc; sum_n += ld * Sn;
         }
         dtau = sum_dtau; Scurr = sum_c / sum_dtau; Snext = sum_n / sum_dtau;
@@ -449,12 +481,11 @@ __device__ __forceinline__ void S_dtau_rec(const DevModel& m, const double4* __r
     const double nb = m.max_dist * (right_freq * sqw_n);
     const double ub = (cb < nb) ? nb : cb;
     const double left = left_freq - ub, right = right_freq + ub;
-    const uint32_t lo = lower_bound_d(m.sorted_line, m.nlines, left);
-    const uint32_t hi = upper_bound_d(m.sorted_line, m.nlines, right);
+    const uint32_t lo = slo + lower_bound_d(m.sorted_line + slo, nsel, left);
+    const uint32_t hi = slo + upper_bound_d(m.sorted_line + slo, nsel, right);
     for (uint32_t sl = lo; sl < hi; sl++) {
         double Sc, Sn;
-        const uint32_t l = __ldg(&m.sorted_map[sl]);
-        const double ld  = dtau_single_line_rec(m, ldg4(&Rc[l]), ldg4(&Rn[l]), l, currfreq, nextfreq, dz, Sc, Sn);
+        const double ld = dtau_single_line_rec(m, ldg4(&Rc[sl - slo]), ldg4(&Rn[sl - slo]), __ldg(&m.sorted_line[sl]), currfreq, nextfreq, dz, Sc, Sn);
         sum_dtau += ld; sum_c += ld * Sc; sum_n += ld * Sn;
     }
     double d = sum_dtau;
@@ -466,23 +497,23 @@ __device__ __forceinline__ void S_dtau_rec(const DevModel& m, const double4* __r
 // compute_source_dtau (solver.tpp:2139-2186) between the positions with headers hc (current) and hn (next)
 template <int APPROX>
 __device__ __forceinline__ void image_source_dtau_rec(const DevModel& m, const double4 hc, const double4 hn, const double4* __restrict__ Rc,
-                                                      const double4* __restrict__ Rn, double freq, bool& compute_curr_opacity, double& dtau_n,
+                                                      const double4* __restrict__ Rn, uint32_t slo, uint32_t nsel, double freq, bool& compute_curr_opacity, double& dtau_n,
                                                       double& chi_c, double& chi_n, double& S_c, double& S_n) {
     const double dshift_abs = fabs(hn.x - hc.x);
     const double dshift_max = (hn.w < hc.w) ? hn.w : hc.w; /* std::min(curr, next) */
     const double curr_freq = freq * hc.x, next_freq = freq * hn.x, dz = hc.y;
     if (dshift_abs > dshift_max) {
         compute_curr_opacity = true;
-        S_dtau_rec<APPROX>(m, Rc, Rn, hc.z, hn.z, curr_freq, next_freq, dz, dtau_n, S_c, S_n);
+        S_dtau_rec<APPROX>(m, Rc, Rn, slo, nsel, hc.z, hn.z, curr_freq, next_freq, dz, dtau_n, S_c, S_n);
     } else {
         if (compute_curr_opacity) {
             compute_curr_opacity = false;
             double eta_c;
-            eta_chi_rec<APPROX>(m, Rc, hc.z, curr_freq, eta_c, chi_c);
+            eta_chi_rec<APPROX>(m, Rc, slo, nsel, hc.z, curr_freq, eta_c, chi_c);
             S_c = ddiv(eta_c, chi_c);
         }
         double eta_n;
-        eta_chi_rec<APPROX>(m, Rn, hn.z, next_freq, eta_n, chi_n);
+        eta_chi_rec<APPROX>(m, Rn, slo, nsel, hn.z, next_freq, eta_n, chi_n);
         S_n    = ddiv(eta_n, chi_n);
         dtau_n = 0.5 * (chi_c + chi_n) * dz;
     }
@@ -503,11 +534,12 @@ struct ImageItems {
 #define MGB_IMAGE_PREFETCH 1
 #endif
 template <int APPROX, bool TAU>
-__global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevModel m, uint32_t npix, uint32_t nfreqs, ImageItems it,
+__global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevModel m, uint32_t pix0, uint32_t npix, uint32_t nfreqs, ImageItems it,
                                                                          const double* __restrict__ nu, uint32_t nu_stride,
                                                                          const uint32_t* __restrict__ len, const uint32_t* __restrict__ start,
                                                                          ImagePaths ip, const double4* __restrict__ hdr,
-                                                                         const double4* __restrict__ rec, double* __restrict__ I) {
+                                                                         const double4* __restrict__ rec, uint32_t slo, uint32_t nsel,
+                                                                         double* __restrict__ I) {
     const unsigned lane = threadIdx.x & 31;
     const size_t item   = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     stage_exp_table();
@@ -525,7 +557,7 @@ __global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevMode
         active = lane < it.group * it.tail && pix_l < npix;
         if (!active) { pix_l = (item - nfull_items) * it.group; f = nfreqs - 1; } /* idle lanes shadow the warp's first pixel */
     }
-    const uint32_t pix = (uint32_t)pix_l;
+    const uint32_t pix = pix0 + (uint32_t)pix_l; /* this launch images the pixels [pix0, pix0 + npix) of the chunk */
     const uint32_t c   = start[pix];
     const uint32_t L   = len[pix];
     const double freq  = __ldg(&nu[(size_t)c * nu_stride + f]);
@@ -535,22 +567,22 @@ __global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevMode
     } else {
         const unsigned long long roff = ip.poff[pix] + pix;
         const uint32_t far_point = ip.nr[entry_offset(ip, pix) + L - 1];
-        const double4* Rc = rec + (roff + L) * m.nlines;
+        const double4* Rc = rec + (roff + L) * nsel;
         double4 hc = ldg4(&hdr[roff + L]), hn = ldg4(&hdr[roff + L - 1]);
         bool compute_curr_opacity = true;
         double chi_c = 0.0, chi_n = 0.0, term_c = 0.0, term_n = 0.0, dtau_n = 0.0, dtau_c, tau = 0.0;
         double Su = 0.0, FF = 0.0, FI = 0.0;
         for (uint32_t e = L; e-- > 0;) { /* current = position e + 1, next = position e */
-            const double4* Rn = Rc - m.nlines;
+            const double4* Rn = Rc - nsel;
 #if MGB_IMAGE_PREFETCH
             const double4 hnn = ldg4(&hdr[roff + (e ? e - 1 : 0)]); /* the header after next, one step ahead of its use */
 #endif
             if (TAU) {
                 if (e != L - 1) { term_c = term_n; chi_c = chi_n; }
-                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, slo, nsel, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
                 tau += dtau_n;
             } else if (e == L - 1) {
-                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, slo, nsel, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
                 const double inverse_dtau_f = drcp(dtau_n);
                 const double Cf        = 2.0 * inverse_dtau_f * inverse_dtau_f;
                 const double Bf_min_Cf = 1.0 + 2.0 * inverse_dtau_f;
@@ -562,7 +594,7 @@ __global__ void __launch_bounds__(128, MGB_IMAGE_CTAS) k_image_solve_rec(DevMode
                 FI = drcp(1.0 + FF);
             } else {
                 term_c = term_n; dtau_c = dtau_n; chi_c = chi_n;
-                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
+                image_source_dtau_rec<APPROX>(m, hc, hn, Rc, Rn, slo, nsel, freq, compute_curr_opacity, dtau_n, chi_c, chi_n, term_c, term_n);
                 const double dtau_avg  = 0.5 * (dtau_c + dtau_n);
                 const double inverse_A = dtau_avg * dtau_c;
                 const double inverse_C = dtau_avg * dtau_n;
@@ -670,6 +702,7 @@ void projection_surface(const mgb_ctx* ctx, int dimension, ImageGeom& g, uint32_
 }
 } // namespace
 
+constexpr size_t kStageMaxBytes = 1ull << 30; // pinned staging of the image result: chunks above this take a plain cudaMemcpy
 #define MGB_TRY_(x) do { int rc_ = (x); if (rc_ != MGB_OK) return rc_; } while (0)
 
 static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
@@ -722,19 +755,28 @@ static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimensio
     MGB_CUDA(ctx, ctx->im_shift0.ensure(8 * (size_t)npix)); MGB_CUDA(ctx, ctx->im_poff.ensure(8 * (size_t)npix));
     MGB_CUDA(ctx, ctx->counters.ensure(64));
     MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.p, 0, 64, ctx->stream));
-    // ---- pixel chunks: bounded entry storage (32 B per entry, + 32 + 32 * nlines with records) and bounded result rows ----
+    MGB_CUDA(ctx, cudaMemsetAsync(ctx->counters.as<unsigned long long>() + 2, 0xff, 8, ctx->stream)); /* the smallest shift */
+    {   /* the largest sqrtw_max of the model (the window of a bin is at most max_dist * freq * that) -> counters[4] */
+        size_t tmp = 0;
+        cub::DeviceReduce::Max(nullptr, tmp, m.sqrtw_max, ctx->counters.as<double>() + 4, (int64_t)m.npoints, ctx->stream);
+        MGB_CUDA(ctx, ctx->cub_tmp.ensure(tmp));
+        MGB_CUDA(ctx, cub::DeviceReduce::Max(ctx->cub_tmp.p, tmp, m.sqrtw_max, ctx->counters.as<double>() + 4, (int64_t)m.npoints, ctx->stream));
+    }
+    // ---- pixel chunks: bounded entry storage (32 B per entry, + 32 + 32 * selected lines with records) and bounded result rows ----
     const char* env_kernel = getenv("MGB_IMAGE_KERNEL"); /* 1: the generic solve kernel, no records, two trace passes */
     const bool generic = env_kernel && env_kernel[0] == '1';
-    const unsigned long long entry_bytes = generic ? 32ull : 64ull + 32ull * m.nlines;
-    const unsigned long long entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / entry_bytes);
+    unsigned long long entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / (generic ? 32ull : 128ull));
     const uint32_t pix_budget = (uint32_t)std::max<size_t>(1, ctx->params.scratch_bytes / (8 * (size_t)nfreqs));
     const uint32_t nchunks_f  = (nfreqs + 31) / 32;
     const unsigned trace_blocks = (unsigned)(((size_t)npix * 32 + 127) / 128);
+    // per-entry buffers grow with a quarter of headroom: the next direction's rays are a little longer or shorter, and a cudaFree +
+    // cudaMalloc of GBs on a full GPU took 0.3 s
+    auto grow = [](mgb::DevBuf& b, size_t n) -> cudaError_t { return (b.p && n <= b.bytes) ? cudaSuccess : b.ensure(n + n / 4); };
     auto ensure_entries = [&](size_t ne) -> cudaError_t {
         cudaError_t e;
-        if ((e = ctx->im_nr.ensure(4 * ne)) != cudaSuccess || (e = ctx->im_nri.ensure(4 * ne)) != cudaSuccess ||
-            (e = ctx->im_fac.ensure(8 * ne)) != cudaSuccess || (e = ctx->im_sh.ensure(8 * ne)) != cudaSuccess ||
-            (e = ctx->im_dz.ensure(8 * ne)) != cudaSuccess) return e;
+        if ((e = grow(ctx->im_nr, 4 * ne)) != cudaSuccess || (e = grow(ctx->im_nri, 4 * ne)) != cudaSuccess ||
+            (e = grow(ctx->im_fac, 8 * ne)) != cudaSuccess || (e = grow(ctx->im_sh, 8 * ne)) != cudaSuccess ||
+            (e = grow(ctx->im_dz, 8 * ne)) != cudaSuccess) return e;
         return cudaSuccess;
     };
     // ---- first pass over the whole pixel range: the entry counts -- and, when a per-pixel capacity derived from the previous image's
@@ -763,9 +805,28 @@ static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimensio
     MGB_CUDA(ctx, cudaGetLastError());
     st.n_launches++;
     st.ms_trace += tt.stop();
-    unsigned long long cnt[2];
-    MGB_CUDA(ctx, cudaMemcpy(cnt, ctx->counters.p, 16, cudaMemcpyDeviceToHost));
+    unsigned long long cnt[5];
+    MGB_CUDA(ctx, cudaMemcpy(cnt, ctx->counters.p, 40, cudaMemcpyDeviceToHost));
     st.n_entries = cnt[0]; st.max_ray_length = (uint32_t)cnt[1];
+    // ---- the lines some bin of this image can have in its window: sorted indices [slo, slo + nsel). A bin at frequency nu sees
+    //      nu * shift -+ max_dist * (nu * shift) * sqrtw_max (solver.tpp:1259-1302, 2012-2111); bounds over all bins, all shifts of the
+    //      traced rays and the largest sqrtw_max, widened by 1e-9 relative (rounding is 1e-16), never miss a line the kernels' own
+    //      searches would find. ApproximationType None sums every line; per-point frequency rows keep every line as well. ----
+    uint32_t slo = 0, nsel = m.nlines;
+    if (!generic && approx == APPROX_CLOSELINES && !nu_per_point && cnt[2] != 0 && cnt[2] != ~0ull && ctx->h_sorted_line.size() == m.nlines) {
+        double sh_min, sh_max, sqw;
+        memcpy(&sh_min, &cnt[2], 8); memcpy(&sh_max, &cnt[3], 8); memcpy(&sqw, &cnt[4], 8);
+        const double nu_min = *std::min_element(nu, nu + nfreqs), nu_max = *std::max_element(nu, nu + nfreqs);
+        if (nu_min > 0.0 && sqw >= 0.0 && std::isfinite(nu_max) && std::isfinite(sqw) && std::isfinite(ctx->m.max_dist) && ctx->m.max_dist >= 0.0) {
+            const double wide = 1.0 + 1.0e-9;
+            const double hi_f = nu_max * sh_max * wide, lo_f = nu_min * sh_min / wide;
+            const double ub = ctx->m.max_dist * hi_f * sqw * wide;
+            const auto& sl = ctx->h_sorted_line;
+            slo  = (uint32_t)(std::lower_bound(sl.begin(), sl.end(), lo_f - ub) - sl.begin());
+            nsel = (uint32_t)(std::upper_bound(sl.begin(), sl.end(), hi_f + ub) - sl.begin()) - slo;
+        }
+    }
+    if (!generic) entry_budget = std::max<unsigned long long>(1ull << 20, ctx->params.path_cache_bytes / (64ull + 32ull * nsel));
     ctx->im_last_max = (uint32_t)cnt[1];
     if (cap && (cnt[1] > cap || cnt[0] + npix > entry_budget)) cap = 0; /* some walk did not fit: count is known, fill in a second pass */
     std::vector<uint32_t> hlen;
@@ -818,26 +879,94 @@ static int image_impl(mgb_ctx* ctx, bool optical_depth, int approx, int dimensio
 #undef MGB_IMAGE_LAUNCH
         } else {
             const size_t npos = ne + np; /* every pixel's entries + its start point */
-            MGB_CUDA(ctx, ctx->im_hdr.ensure(32 * npos));
-            MGB_CUDA(ctx, ctx->im_rec.ensure(32 * npos * m.nlines));
-            ImageRecs ir{ctx->im_hdr.as<double4>(), ctx->im_rec.as<double4>()};
-            k_image_records<<<(unsigned)(((size_t)np * 32 + 127) / 128), 128, 0, ctx->stream>>>(
-                m, np, len_c, ctx->im_start.as<uint32_t>() + p0, ctx->im_shift0.as<double>() + p0, ip, ir);
+            MGB_CUDA(ctx, grow(ctx->im_hdr, 32 * npos));
+            MGB_CUDA(ctx, grow(ctx->im_rec, 32 * npos * std::max(nsel, 1u)));
+            ImageRecs ir{ctx->im_hdr.as<double4>(), ctx->im_rec.as<double4>(), slo, nsel};
+            const unsigned kblocks = (unsigned)(((size_t)np * 32 + 127) / 128);
+            if (approx == APPROX_CLOSELINES)
+                k_image_records<true><<<kblocks, 128, 0, ctx->stream>>>(m, np, len_c, ctx->im_start.as<uint32_t>() + p0,
+                                                                        ctx->im_shift0.as<double>() + p0, ip, ir);
+            else
+                k_image_records<false><<<kblocks, 128, 0, ctx->stream>>>(m, np, len_c, ctx->im_start.as<uint32_t>() + p0,
+                                                                         ctx->im_shift0.as<double>() + p0, ip, ir);
             MGB_CUDA(ctx, cudaGetLastError());
             st.n_launches++;
             ImageItems it{nfreqs / 32, nfreqs % 32, (nfreqs % 32) ? 32 / (nfreqs % 32) : 0};
-            const unsigned rblocks = (unsigned)((it.count(np) * 32 + 127) / 128);
+            // The chunk is solved in slices of pixels: slice k goes device -> pinned staging on the copy stream while slice k + 1 is
+            // solved, and host threads move the staged slices into the caller's buffer (a plain cudaMemcpy of 210 MB into pageable
+            // memory took longer than the kernels).
+            const size_t chunk_bytes = 8 * (size_t)np * nfreqs;
+            const bool staged = chunk_bytes <= kStageMaxBytes;
+            const uint32_t nslices = (staged && np >= 8192) ? 8u : 1u;
+            const uint32_t align = it.group ? it.group : 1u;
+            std::vector<cudaEvent_t> ev(staged ? 2 * nslices : 0, nullptr);
+            std::vector<uint32_t> cut(nslices + 1, 0);
+            for (uint32_t k = 1; k < nslices; k++) cut[k] = (uint32_t)((size_t)np * k / nslices) / align * align;
+            cut[nslices] = np;
+            cudaError_t perr = cudaSuccess;
+            if (staged) {
+                if ((perr = ctx->im_stage.ensure(chunk_bytes)) == cudaSuccess && !ctx->im_copy_stream.s)
+                    perr = cudaStreamCreateWithFlags(&ctx->im_copy_stream.s, cudaStreamNonBlocking);
+                for (auto& e : ev)
+                    if (perr == cudaSuccess) perr = cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+            }
+            auto drop_events = [&] { for (auto e : ev) if (e) cudaEventDestroy(e); };
+            if (perr != cudaSuccess) { drop_events(); MGB_CUDA(ctx, perr); }
+            for (uint32_t k = 0; k < nslices && perr == cudaSuccess; k++) {
+                const uint32_t a = cut[k], ns = cut[k + 1] - cut[k];
+                if (ns) {
+                    const unsigned rblocks = (unsigned)((it.count(ns) * 32 + 127) / 128);
 #define MGB_IMAGE_LAUNCH(A, T)                                                                                                          \
-    k_image_solve_rec<A, T><<<rblocks, 128, 0, ctx->stream>>>(m, np, nfreqs, it, ctx->im_nu.as<double>(), stride, len_c,                \
-                                                              ctx->im_start.as<uint32_t>() + p0, ip, ir.hdr, ir.rec, ctx->im_I.as<double>())
-            if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
-            else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
+    k_image_solve_rec<A, T><<<rblocks, 128, 0, ctx->stream>>>(m, a, ns, nfreqs, it, ctx->im_nu.as<double>(), stride, len_c,             \
+                                                              ctx->im_start.as<uint32_t>() + p0, ip, ir.hdr, ir.rec, ir.slo, ir.nsel, ctx->im_I.as<double>())
+                    if (approx == APPROX_NONE) { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_NONE, true); else MGB_IMAGE_LAUNCH(APPROX_NONE, false); }
+                    else { if (optical_depth) MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, true); else MGB_IMAGE_LAUNCH(APPROX_CLOSELINES, false); }
 #undef MGB_IMAGE_LAUNCH
+                    perr = cudaGetLastError();
+                    st.n_launches++;
+                }
+                if (staged && perr == cudaSuccess) {
+                    const size_t off = (size_t)a * nfreqs;
+                    if ((perr = cudaEventRecord(ev[2 * k], ctx->stream)) == cudaSuccess &&
+                        (perr = cudaStreamWaitEvent(ctx->im_copy_stream.s, ev[2 * k], 0)) == cudaSuccess &&
+                        (ns == 0 || (perr = cudaMemcpyAsync((double*)ctx->im_stage.p + off, ctx->im_I.as<double>() + off, 8 * (size_t)ns * nfreqs,
+                                                            cudaMemcpyDeviceToHost, ctx->im_copy_stream.s)) == cudaSuccess))
+                        perr = cudaEventRecord(ev[2 * k + 1], ctx->im_copy_stream.s);
+                }
+            }
+            if (perr != cudaSuccess) { cudaStreamSynchronize(ctx->stream); if (staged) cudaStreamSynchronize(ctx->im_copy_stream.s); drop_events(); MGB_CUDA(ctx, perr); }
+            if (staged) {
+                const unsigned nthreads = std::max(1u, std::min(8u, std::thread::hardware_concurrency()));
+                std::vector<cudaError_t> werr(nthreads, cudaSuccess);
+                std::vector<std::thread> workers;
+                const int device = ctx->device;
+                const double* stage = (const double*)ctx->im_stage.p;
+                double* dst = I_out + (size_t)p0 * nfreqs;
+                for (unsigned t = 0; t < nthreads; t++)
+                    workers.emplace_back([&, t] {
+                        cudaSetDevice(device);
+                        for (uint32_t k = 0; k < nslices; k++) {
+                            const cudaError_t e = cudaEventSynchronize(ev[2 * k + 1]);
+                            if (e != cudaSuccess) { werr[t] = e; return; }
+                            const size_t n = (size_t)(cut[k + 1] - cut[k]) * nfreqs, b = n * t / nthreads, c = n * (t + 1) / nthreads;
+                            memcpy(dst + (size_t)cut[k] * nfreqs + b, stage + (size_t)cut[k] * nfreqs + b, 8 * (c - b));
+                        }
+                    });
+                st.ms_solve += tt.stop(); /* the kernels; the workers drain the slices meanwhile */
+                for (auto& w : workers) w.join();
+                drop_events();
+                for (auto e : werr) MGB_CUDA(ctx, e);
+            } else {
+                st.ms_solve += tt.stop();
+                MGB_CUDA(ctx, cudaMemcpy(I_out + (size_t)p0 * nfreqs, ctx->im_I.p, chunk_bytes, cudaMemcpyDeviceToHost));
+            }
         }
-        MGB_CUDA(ctx, cudaGetLastError());
-        st.n_launches++;
-        st.ms_solve += tt.stop();
-        MGB_CUDA(ctx, cudaMemcpy(I_out + (size_t)p0 * nfreqs, ctx->im_I.p, 8 * (size_t)np * nfreqs, cudaMemcpyDeviceToHost));
+        if (generic) {
+            MGB_CUDA(ctx, cudaGetLastError());
+            st.n_launches++;
+            st.ms_solve += tt.stop();
+            MGB_CUDA(ctx, cudaMemcpy(I_out + (size_t)p0 * nfreqs, ctx->im_I.p, 8 * (size_t)np * nfreqs, cudaMemcpyDeviceToHost));
+        }
         st.n_chunks++;
         p0 = p1;
     }
