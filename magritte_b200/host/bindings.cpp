@@ -180,6 +180,16 @@ PYBIND11_MODULE(core, m) {
                     }
             }
         }, py::arg("J"), py::arg("lam"), py::arg("cnt"), py::arg("J_lines") = py::none())
+        // test hook, n_off_diag > 0: radiation.J and the banded Lambda lists [npoints][nlines][cap] (insertion order) of a radiation-field call
+        .def("set_radiation_field_lists", [](Model& s, arr<double> J, arr<double> val, arr<uint32_t> nr, arr<uint32_t> cnt) {
+            s.J = vec(J);
+            const size_t rows = (size_t)s.npoints * s.nlines();
+            if ((size_t)cnt.size() != rows || val.size() != nr.size() || rows == 0 || (size_t)val.size() % rows) throw std::runtime_error("set_radiation_field_lists: shapes");
+            s.set_lambda_lists(val.data(), nr.data(), cnt.data(), (size_t)val.size() / rows);
+        }, py::arg("J"), py::arg("val"), py::arg("nr"), py::arg("cnt"))
+        .def("stateq_solver_info", [](const Model& s, size_t l) { /* (Krylov iterations, final residual) of the last banded statistical-equilibrium solve */
+            return py::make_tuple(s.lineProducingSpecies.at(l).stateq_iterations, (double)s.lineProducingSpecies.at(l).stateq_residual);
+        })
         // results (copies, reference layouts)
         .def("get_J", [](const Model& s) { return out2(s.J, s.npoints, s.nfreqs); })
         .def("get_nu", [](const Model& s) { return out2(s.nu, s.npoints, s.nfreqs); })

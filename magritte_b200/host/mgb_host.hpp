@@ -15,10 +15,14 @@
 // The statistical-equilibrium system of the reference is one global sparse LU (Eigen::SparseLU, long double). With the
 // diagonal Lambda operator of this path (n_off_diag = 0) it is block diagonal -- one nlev x nlev block per point -- and is
 // solved here block by block with a dense long-double LU with partial pivoting: same equations, different pivot order.
+// With a banded Lambda operator (n_off_diag > 0) the blocks couple; the same global system is then solved in long double by
+// iterative refinement on the original equations with block-Jacobi preconditioned GMRES corrections, down to a component-wise
+// backward error of a few long-double epsilons (LineProducingSpecies::solve_statistical_equilibrium_banded).
 #pragma once
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
 #include <ctime>
 #include <limits>
 #include <memory>
@@ -141,6 +145,38 @@ inline bool lu_solve(std::vector<LD>& A, std::vector<LD>& b, const Size n) {
     return true;
 }
 
+// The same factorisation kept for repeated solves: A [n][n] row-major -> L\U in place, piv [n]. false on a zero pivot.
+inline bool lu_factor(LD* A, Size* piv, const Size n) {
+    for (Size c = 0; c < n; c++) {
+        Size pr = c;
+        LD big = fabsl(A[(size_t)c * n + c]);
+        for (Size r = c + 1; r < n; r++) if (fabsl(A[(size_t)r * n + c]) > big) { big = fabsl(A[(size_t)r * n + c]); pr = r; }
+        if (big == 0.0L) return false;
+        piv[c] = pr;
+        if (pr != c) for (Size k = 0; k < n; k++) std::swap(A[(size_t)c * n + k], A[(size_t)pr * n + k]);
+        const LD inv = 1.0L / A[(size_t)c * n + c];
+        for (Size r = c + 1; r < n; r++) {
+            const LD f = A[(size_t)r * n + c] * inv;
+            A[(size_t)r * n + c] = f;
+            if (f == 0.0L) continue;
+            for (Size k = c + 1; k < n; k++) A[(size_t)r * n + k] -= f * A[(size_t)c * n + k];
+        }
+    }
+    return true;
+}
+inline void lu_apply(const LD* A, const Size* piv, LD* b, const Size n) {
+    for (Size c = 0; c < n; c++) {
+        if (piv[c] != c) std::swap(b[c], b[piv[c]]);
+        const LD bc = b[c];
+        if (bc != 0.0L) for (Size r = c + 1; r < n; r++) b[r] -= A[(size_t)r * n + c] * bc;
+    }
+    for (Size r = n; r-- > 0;) {
+        LD t = b[r];
+        for (Size k = r + 1; k < n; k++) t -= A[(size_t)r * n + k] * b[k];
+        b[r] = t / A[(size_t)r * n + r];
+    }
+}
+
 // Least-squares / square solve by Householder QR with column pivoting (what RTR.colPivHouseholderQr().solve(ones) does in the
 // reference's Ng acceleration, lineProducingSpecies.tpp:300-302); rank decided with Eigen's default threshold n * epsilon.
 inline VecLD colpiv_qr_solve(std::vector<LD> A, VecLD b, const Size n) {
@@ -196,6 +232,13 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
     std::vector<Real> J2_0, J2_1_Re, J2_1_Im, J2_2_Re, J2_2_Im; // [npoints][nrad] anisotropic radiation-field tensor (lineProducingSpecies.hpp:29-35)
     std::vector<Real> lambda_Ls;             // [npoints][nrad] the diagonal ALO element (nr == p), lambda.tpp:79-89
     std::vector<Size> lambda_cnt;            // [npoints][nrad] list length (0 or 1)
+    // n_off_diag > 0: the whole (p, k) lists of Lambda::add_element (lambda.tpp:79-89) in insertion order, CSR over (p, k)
+    bool banded = false;
+    std::vector<size_t> ll_off;              // [npoints * nrad + 1]
+    std::vector<Size> ll_nr;                 // Lambda.nr[p][k][m]
+    std::vector<Real> ll_Ls;                 // Lambda.Ls[p][k][m]
+    int stateq_iterations = 0;               // Krylov iterations of the last banded statistical-equilibrium solve
+    LD stateq_residual = 0;                  // its final preconditioned residual (max norm, in units of the point's total population)
     Real fraction_not_converged = 0, relative_change_mean = 0, relative_change_max = 0;
 
     Size index(const Size p, const Size i) const { return i + p * linedata.nlev; }
@@ -337,6 +380,7 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         population_prev3 = population_prev2; population_prev2 = population_prev1; population_prev1 = population;
         residuals.push_back(diff(population, populations.back()));
         populations.push_back(population);
+        if (banded && !sparse) { solve_statistical_equilibrium_banded(abundance, nspecs, temperature); return; }
         bool failed = false;
 #pragma omp parallel
         {
@@ -387,6 +431,192 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
             }
         }
         if (failed) throw std::runtime_error("Eigen solver ERROR."); /* same text as lineProducingSpecies.tpp:551 */
+    }
+    // lineProducingSpecies.tpp:377-581 with a banded Lambda operator: the off-diagonal elements couple level irad of point nr to the
+    // rate equation of level jrad at point p, so the system is one global sparse matrix A (npoints * nlev unknowns), which the
+    // reference hands to Eigen::SparseLU in long double. Here: the same equations, assembled as the per-point nlev x nlev blocks D_p
+    // plus a list of off-block entries O; unknowns scaled to fractions of the point's total population; solved by restarted GMRES
+    // in long double on the block-Jacobi preconditioned system D^-1 (D + O) f = D^-1 y, started from the block-diagonal solution and
+    // run until the preconditioned residual (i.e. the error estimate in fraction units) reaches long-double rounding level.
+    void solve_statistical_equilibrium_banded(const std::vector<Real>& abundance, const Size nspecs, const std::vector<Real>& temperature) {
+        const Size nlev = linedata.nlev, nrad = linedata.nrad;
+        const size_t B = (size_t)nlev * nlev, n = (size_t)npoints * nlev;
+        std::vector<LD> D(B * npoints, 0.0L);
+        std::vector<Size> piv(n);
+        VecLD y(n, 0.0L);
+        std::vector<LD> scale(npoints);
+        for (Size p = 0; p < npoints; p++) scale[p] = population_tot[p] > 0.0 ? (LD)population_tot[p] : 1.0L;
+        // ---- local parts of the blocks (radiative, collisional, conservation row), as in the block-diagonal path ----
+#pragma omp parallel
+        {
+            std::vector<CollisionPartner> cps = linedata.colpar;
+#pragma omp for schedule(static)
+            for (Size p = 0; p < npoints; p++) {
+                LD* M = &D[B * p];
+                auto add = [&](Size r, Size c, LD v) { M[(size_t)r * nlev + c] += v; };
+                for (Size k = 0; k < nrad; k++) {
+                    const LD v_IJ = linedata.A[k] + linedata.Bs[k] * Jeff[(size_t)p * nrad + k];
+                    const LD v_JI = linedata.Ba[k] * Jeff[(size_t)p * nrad + k];
+                    const Size I = linedata.irad[k], J = linedata.jrad[k];
+                    if (J != nlev - 1) { add(J, I, +v_IJ); add(J, J, -v_JI); }
+                    if (I != nlev - 1) { add(I, J, +v_JI); add(I, I, -v_IJ); }
+                }
+                for (CollisionPartner& colpar : cps) {
+                    Real abn = abundance[(size_t)p * nspecs + colpar.num_col_partner];
+                    Real tmp = temperature[p];
+                    colpar.adjust_abundance_for_ortho_or_para(tmp, abn);
+                    colpar.interpolate_collision_coefficients(tmp);
+                    for (Size k = 0; k < colpar.icol.size(); k++) {
+                        const LD v_IJ = colpar.Cd_intpld[k] * abn;
+                        const LD v_JI = colpar.Ce_intpld[k] * abn;
+                        const Size I = colpar.icol[k], J = colpar.jcol[k];
+                        if (J != nlev - 1) { add(J, I, +v_IJ); add(J, J, -v_JI); }
+                        if (I != nlev - 1) { add(I, J, +v_JI); add(I, I, -v_IJ); }
+                    }
+                }
+                for (Size i = 0; i < nlev; i++) add(nlev - 1, i, 1.0L);
+                y[index(p, nlev - 1)] = population_tot[p];
+            }
+        }
+        // ---- the approximated Lambda operator (:439-460): (J = (p, jrad), I = (nr, irad)) += v, (I, I) -= v with I at point nr ----
+        struct Off { Size row, nr, col; LD v; }; /* row level at point p, column level at point nr */
+        std::vector<size_t> o_off(npoints + 1, 0);
+        std::vector<Off> offs;
+        for (Size p = 0; p < npoints; p++) {
+            for (Size k = 0; k < nrad; k++) {
+                const Real freq = linedata.frequency[k];
+                const Real opac = get_opacity(p, k);
+                for (size_t m = ll_off[(size_t)p * nrad + k]; m < ll_off[(size_t)p * nrad + k + 1]; m++) {
+                    const Size nr   = ll_nr[m];
+                    const LD v_IJ   = -ll_Ls[m] * opac / freq;
+                    const Size I = linedata.irad[k], J = linedata.jrad[k];
+                    if (J != nlev - 1) {
+                        if (nr == p) D[B * p + (size_t)J * nlev + I] += v_IJ;
+                        else offs.push_back(Off{J, nr, I, v_IJ});
+                    }
+                    if (I != nlev - 1) D[B * nr + (size_t)I * nlev + I] -= v_IJ; /* a diagonal element of point nr's block */
+                }
+            }
+            o_off[p + 1] = offs.size();
+        }
+        // ---- unknowns as fractions of the point's total: column scaling of every block and off-block entry; right-hand side -> 1 ----
+#pragma omp parallel for schedule(static)
+        for (Size p = 0; p < npoints; p++) {
+            for (size_t e = 0; e < B; e++) D[B * p + e] *= scale[p];
+            for (size_t e = o_off[p]; e < o_off[p + 1]; e++) offs[e].v *= scale[offs[e].nr];
+        }
+        std::vector<LD> Dm = D; /* the blocks themselves (matrix-vector products); D becomes their LU factors */
+        bool failed = false;
+#pragma omp parallel for schedule(static)
+        for (Size p = 0; p < npoints; p++)
+            if (!lu_factor(&D[B * p], &piv[(size_t)p * nlev], nlev)) failed = true;
+        if (failed) throw std::runtime_error("Eigen solver ERROR."); /* same text as lineProducingSpecies.tpp:551 */
+        auto precond = [&](VecLD& v) { /* v <- D^-1 v */
+#pragma omp parallel for schedule(static)
+            for (Size p = 0; p < npoints; p++) lu_apply(&D[B * p], &piv[(size_t)p * nlev], &v[(size_t)p * nlev], nlev);
+        };
+        auto applyA = [&](const VecLD& f, VecLD& out, VecLD* mag) { /* out <- (D + O) f; mag <- (|D| + |O|) |f| when asked for */
+#pragma omp parallel for schedule(static)
+            for (Size p = 0; p < npoints; p++) {
+                const LD* M = &Dm[B * p];
+                for (Size r = 0; r < nlev; r++) {
+                    LD t = 0.0L, a = 0.0L;
+                    for (Size c = 0; c < nlev; c++) { const LD x = M[(size_t)r * nlev + c] * f[(size_t)p * nlev + c]; t += x; a += fabsl(x); }
+                    out[(size_t)p * nlev + r] = t;
+                    if (mag) (*mag)[(size_t)p * nlev + r] = a;
+                }
+                for (size_t e = o_off[p]; e < o_off[p + 1]; e++) {
+                    const LD x = offs[e].v * f[(size_t)offs[e].nr * nlev + offs[e].col];
+                    out[(size_t)p * nlev + offs[e].row] += x;
+                    if (mag) (*mag)[(size_t)p * nlev + offs[e].row] += fabsl(x);
+                }
+            }
+        };
+        auto dotp = [&](const VecLD& a, const VecLD& b) {
+            LD t = 0.0L;
+#pragma omp parallel for schedule(static) reduction(+ : t)
+            for (size_t i = 0; i < n; i++) t += a[i] * b[i];
+            return t;
+        };
+        // ---- iterative refinement on the ORIGINAL equations: r = y - A f in long double, component-wise backward error
+        //      omega = max_i |r_i| / ((|A| |f|)_i + |y_i|) (Oettli-Prager: f solves a system whose every entry is off by at most omega
+        //      relative -- what a backward-stable direct solver delivers at omega ~ epsilon); the correction A d = r is solved by one
+        //      GMRES(restart) cycle on the block-Jacobi preconditioned system. The blocks can be badly conditioned (a point collects the
+        //      Lambda elements of every list that names it), which is why convergence is NOT judged on the preconditioned residual. ----
+        VecLD f = y;
+        precond(f); /* start: the block-diagonal solution */
+        VecLD r(n), w(n), mag(n);
+        const int restart = 40, max_outer = 80;
+        const LD eps = std::numeric_limits<LD>::epsilon(), tol = 8.0L * eps;
+        std::vector<VecLD> V;
+        std::vector<std::vector<LD>> H(restart + 1, std::vector<LD>(restart, 0.0L));
+        std::vector<LD> cs(restart), sn(restart), g(restart + 1);
+        stateq_iterations = 0;
+        LD omega = 0.0L, best = std::numeric_limits<LD>::infinity();
+        VecLD fbest;
+        int since_best = 0;
+        const bool debug = getenv("MGBH_STATEQ_DEBUG") != nullptr;
+        for (int outer = 0; outer <= max_outer; outer++) {
+            applyA(f, w, &mag);
+            omega = 0.0L;
+            for (size_t i = 0; i < n; i++) {
+                r[i] = y[i] - w[i];
+                const LD den = mag[i] + fabsl(y[i]);
+                if (r[i] != 0.0L) omega = std::max(omega, den > 0.0L ? fabsl(r[i]) / den : std::numeric_limits<LD>::infinity());
+            }
+            if (debug) fprintf(stderr, "[stateq] refinement step %d, Krylov iterations %d, backward error %.3Le\n", outer, stateq_iterations, omega);
+            if (omega < best) { best = omega; fbest = f; since_best = 0; } else since_best++;
+            if (best <= tol || outer == max_outer || since_best >= 3) break;
+            precond(r); /* right-hand side of the preconditioned correction equation */
+            const LD beta = sqrtl(dotp(r, r));
+            if (!(beta > 0.0L)) break;
+            V.assign(1, r);
+            for (LD& x : V[0]) x /= beta;
+            std::fill(g.begin(), g.end(), 0.0L);
+            g[0] = beta;
+            int j = 0;
+            for (; j < restart; j++) {
+                applyA(V[j], w, nullptr);
+                precond(w);
+                stateq_iterations++;
+                for (int pass = 0; pass < 2; pass++) /* modified Gram-Schmidt, twice */
+                    for (int i = 0; i <= j; i++) {
+                        const LD h = dotp(w, V[i]);
+                        if (pass == 0) H[i][j] = h; else H[i][j] += h;
+                        for (size_t q = 0; q < n; q++) w[q] -= h * V[i][q];
+                    }
+                H[j + 1][j] = sqrtl(dotp(w, w));
+                for (int i = 0; i < j; i++) { /* the previous Givens rotations on the new column */
+                    const LD t = cs[i] * H[i][j] + sn[i] * H[i + 1][j];
+                    H[i + 1][j] = -sn[i] * H[i][j] + cs[i] * H[i + 1][j];
+                    H[i][j] = t;
+                }
+                const LD den = sqrtl(H[j][j] * H[j][j] + H[j + 1][j] * H[j + 1][j]);
+                if (den == 0.0L) { j++; break; }
+                cs[j] = H[j][j] / den; sn[j] = H[j + 1][j] / den;
+                H[j][j] = den;
+                g[j + 1] = -sn[j] * g[j];
+                g[j] = cs[j] * g[j];
+                const bool breakdown = H[j + 1][j] == 0.0L;
+                if (!breakdown) { V.push_back(w); for (LD& x : V.back()) x /= H[j + 1][j]; }
+                H[j + 1][j] = 0.0L;
+                if (breakdown || fabsl(g[j + 1]) <= 1.0e-10L * beta) { j++; break; }
+            }
+            std::vector<LD> yk(j, 0.0L);
+            for (int i = j; i-- > 0;) {
+                LD t = g[i];
+                for (int k = i + 1; k < j; k++) t -= H[i][k] * yk[k];
+                yk[i] = t / H[i][i];
+            }
+            for (int i = 0; i < j; i++)
+                for (size_t q = 0; q < n; q++) f[q] += yk[i] * V[i][q];
+        }
+        if (!fbest.empty()) f.swap(fbest);
+        stateq_residual = best;
+        if (!(best <= 1.0e-15L))
+            throw std::runtime_error("Eigen solver ERROR."); /* the banded system did not converge */
+        for (Size p = 0; p < npoints; p++)
+            for (Size i = 0; i < nlev; i++) population[index(p, i)] = f[(size_t)p * nlev + i] * scale[p];
     }
     // lineProducingSpecies.tpp:711-802
     void correct_negative_populations(const std::vector<Real>& temperature) {
@@ -646,16 +876,52 @@ class Model {
     }
     // ---- Model::compute_radiation_field_feautrier_order_2 (model.cpp:353-390) -> the C ABI ----
     int compute_radiation_field_feautrier_order_2() {
-        if (parameters.n_off_diag)
-            throw std::runtime_error("magritte_b200.core: n_off_diag > 0 couples the rate equations of neighbouring points (one global sparse system, "
-                                     "lineProducingSpecies.tpp:377-581); the host layer solves the block-diagonal case only. The banded Lambda "
-                                     "lists are available from the C ABI (mgb_get_lambda_lists).");
         run_radiation_field(true);
-        fetch_J_and_lambda();
+        if (parameters.n_off_diag) fetch_J_and_lambda_lists(); /* banded Lambda: the lists couple neighbouring points (host statistical equilibrium) */
+        else fetch_J_and_lambda();
         return 0;
+    }
+    // The banded lists [npoints][nlines][cap] (unused tail ignored) -> every species' CSR lists; lambda_Ls / lambda_cnt keep the
+    // diagonal element and the list length, as mgb_get_lambda reports them for n_off_diag > 0.
+    void set_lambda_lists(const double* val, const uint32_t* nr, const uint32_t* cnt, const size_t cap) {
+        const Size L = nlines();
+        for (Size l = 0; l < nlspecs(); l++) {
+            auto& ls = lineProducingSpecies[l];
+            const Size nrad = ls.linedata.nrad;
+            ls.banded = true;
+            ls.ll_off.assign((size_t)npoints * nrad + 1, 0);
+            ls.ll_nr.clear(); ls.ll_Ls.clear();
+            for (Size p = 0; p < npoints; p++)
+                for (Size k = 0; k < nrad; k++) {
+                    const size_t row = (size_t)p * L + nrad_cum[l] + k;
+                    const Size c = cnt[row];
+                    if (c > cap) throw std::runtime_error("Lambda list longer than its capacity.");
+                    ls.lambda_cnt[(size_t)p * nrad + k] = c;
+                    ls.lambda_Ls[(size_t)p * nrad + k]  = 0.0;
+                    for (Size m = 0; m < c; m++) {
+                        ls.ll_nr.push_back(nr[row * cap + m]);
+                        ls.ll_Ls.push_back(val[row * cap + m]);
+                        if (nr[row * cap + m] >= npoints) throw std::runtime_error("Lambda list names a point outside the model.");
+                        if (nr[row * cap + m] == p) ls.lambda_Ls[(size_t)p * nrad + k] = val[row * cap + m];
+                    }
+                    ls.ll_off[(size_t)p * nrad + k + 1] = ls.ll_nr.size();
+                }
+        }
+    }
+    void fetch_J_and_lambda_lists() {
+        J.resize((size_t)npoints * nfreqs);
+        check(mgb_get_J(ctx, 0, npoints, J.data()), "mgb_get_J");
+        uint32_t cap = 0;
+        check(mgb_lambda_capacity(ctx, &cap), "mgb_lambda_capacity");
+        const size_t rows = (size_t)npoints * nlines();
+        std::vector<double> val(rows * cap);
+        std::vector<uint32_t> nr(rows * cap), cnt(rows);
+        check(mgb_get_lambda_lists(ctx, 0, npoints, val.data(), nr.data(), cnt.data()), "mgb_get_lambda_lists");
+        set_lambda_lists(val.data(), nr.data(), cnt.data(), cap);
     }
     void fetch_J_and_lambda() {
         const Size L = nlines();
+        for (auto& ls : lineProducingSpecies) ls.banded = false;
         J.resize((size_t)npoints * nfreqs);
         std::vector<double> lam((size_t)npoints * L);
         std::vector<uint32_t> cnt((size_t)npoints * L);
@@ -756,6 +1022,12 @@ class Model {
                     Real jl = 0.0;
                     for (Size z = 0; z < nq; z++) jl += lspec.quadrature_weights[z] * J[(size_t)p * nfreqs + (size_t)(nrad_cum[l] + k) * nq + z];
                     double diff = 0.0;
+                    if (lspec.banded) { /* the whole list: neighbouring points' populations enter (model.cpp:531-536) */
+                        for (size_t m = lspec.ll_off[(size_t)p * nrad + k]; m < lspec.ll_off[(size_t)p * nrad + k + 1]; m++) {
+                            const Size I = lspec.index(lspec.ll_nr[m], lspec.linedata.irad[k]);
+                            diff += lspec.ll_Ls[m] * lspec.population[I];
+                        }
+                    } else
                     for (Size m = 0; m < lspec.lambda_cnt[(size_t)p * nrad + k]; m++) {
                         const Size I = lspec.index(p, lspec.linedata.irad[k]);
                         diff += lspec.lambda_Ls[(size_t)p * nrad + k] * lspec.population[I];
@@ -834,7 +1106,8 @@ class Model {
     }
     int level_population_loop(const bool use_Ng_acceleration, const long max_niterations, const bool sparse) {
         if (spectralDiscretisation != SD_Lines) throw std::runtime_error("Spectral discretisation was not set for Lines!");
-        if (device_level_populations) return level_population_loop_device(use_Ng_acceleration, max_niterations, sparse);
+        /* the device twin of the level-population half solves block by block: a banded Lambda operator (one global system) takes the host path */
+        if (device_level_populations && !(parameters.n_off_diag && !sparse && !shortchar)) return level_population_loop_device(use_Ng_acceleration, max_niterations, sparse);
         int iteration = 0, iteration_normal = 0;
         error_mean.clear(); error_max.clear();
         bool some_not_converged = true;

@@ -46,6 +46,28 @@ def test_default_adaptive_Ng_run(name):
         assert np.all(np.abs(got - want) <= 1e-6 * np.abs(want) + 1e-12 * tot), name
 
 
+@pytest.mark.parametrize("name", ["c1_all_constant", "c2_vanzadelhoff", "wind3d_small", "wind3d_spiral_2spec"])
+def test_banded_lambda_iterations(name):
+    """parameters.n_off_diag > 0 through the host Model: the radiation field's banded Lambda lists come from the GPU
+    (mgb_get_lambda_lists), Jeff and the GLOBAL statistical-equilibrium system (neighbouring points couple) are solved on the host
+    (block-Jacobi preconditioned GMRES in long double); K iterations against the compiled reference's SparseLU loop
+    (tests/golden/offdiag_levelpop_*.npz)."""
+    import os
+    m, flat, ref, lp = prepared(name)
+    gold = np.load(os.path.join(util.GOLDEN, f"offdiag_levelpop_{name}.npz"))
+    P = m.mutable_parameters()
+    P.use_adaptive_Ng_acceleration = False
+    P.n_off_diag = int(gold["n_off_diag"])
+    K = int(gold["iterations"])
+    it = m.compute_level_populations(False, K)
+    assert it == K
+    for l in range(int(gold["nspecies"])):
+        # 1e-13 of the point's total: see test_banded_level_population_loop_driven_by_the_oracle (tests/test_host_model.py)
+        assert_populations_close(m.get_population(l), gold[f"final_population_{l}"], m.get_population_tot(l), name, abs_tot=1e-13)
+        assert m.stateq_solver_info(l)[1] <= 1e-17
+    assert np.allclose(m.error_max, gold["final_error_max"], rtol=1e-8, atol=1e-14)
+
+
 def test_image_through_host_model():
     m, flat, ref, lp = prepared("wind3d_small")
     fl, img = util.load_golden_image("wind3d_small")
