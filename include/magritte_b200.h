@@ -197,7 +197,10 @@ typedef struct mgb_image_stats {
  * its start point, solver.tpp:611-614). Pixels [pix_begin, pix_end) of the nx*ny image (index y + ny*x) are computed.
  * Outputs (host): ImX, ImY [nx*ny] (may be NULL), I [(pix_end-pix_begin)][nfreqs]. Needs geometry, thermodynamics, lines and
  * line state; errors mirror the reference's exceptions: zero direction, OneLine (not supported for imaging), and a 1D
- * model imaged along anything but (0,1,0) (image.cpp:80-86) return MGB_EINVAL / MGB_EUNSUPPORTED with the same text. */
+ * model imaged along anything but (0,1,0) (image.cpp:80-86) return MGB_EINVAL / MGB_EUNSUPPORTED with the same text.
+ * Host side of a call: I may be ordinary pageable memory -- the image leaves the device in slices through a pinned staging buffer
+ * of the context (at most 1 GiB, allocated on first use, freed by mgb_destroy) and up to 8 short-lived host threads copy the
+ * slices on while the next slice is solved. The call is synchronous: I is complete when it returns. */
 int mgb_image_feautrier_order_2(mgb_ctx* ctx, int approx, int dimension, const double* ray_dir, uint32_t nx, uint32_t ny,
                                 uint32_t nfreqs, const double* nu, int nu_per_point, uint64_t pix_begin, uint64_t pix_end,
                                 double* ImX, double* ImY, double* I, mgb_image_stats* stats);
