@@ -177,6 +177,46 @@ inline void lu_apply(const LD* A, const Size* piv, LD* b, const Size n) {
     }
 }
 
+// Band matrix (kl sub-, ku super-diagonals) in LAPACK band storage with room for the fill of row pivoting: element (i, j) at
+// AB[(kl + ku + i - j) + ldab * j], ldab = 2 kl + ku + 1. LU with partial pivoting (the unblocked dgbtf2 scheme) and the solve of
+// one right-hand side, in place. false on a zero pivot.
+inline bool band_lu_solve(std::vector<LD>& AB, const size_t n, const size_t kl, const size_t ku, std::vector<LD>& b) {
+    const size_t kv = kl + ku, ldab = 2 * kl + ku + 1;
+    std::vector<size_t> ipiv(n);
+    auto at = [&](size_t i, size_t j) -> LD& { return AB[(kv + i - j) + ldab * j]; };
+    size_t ju = 0;
+    for (size_t j = 0; j < n; j++) {
+        const size_t km = std::min(kl, n - 1 - j);
+        size_t jp = 0;
+        LD big = fabsl(at(j, j));
+        for (size_t i = 1; i <= km; i++) if (fabsl(at(j + i, j)) > big) { big = fabsl(at(j + i, j)); jp = i; }
+        ipiv[j] = j + jp;
+        if (big == 0.0L) return false;
+        ju = std::max(ju, std::min(j + ku + jp, n - 1));
+        if (jp) for (size_t c = j; c <= ju; c++) std::swap(at(j, c), at(j + jp, c));
+        const LD inv = 1.0L / at(j, j);
+        for (size_t i = 1; i <= km; i++) at(j + i, j) *= inv;
+        for (size_t c = j + 1; c <= ju; c++) {
+            const LD u = at(j, c);
+            if (u == 0.0L) continue;
+            for (size_t i = 1; i <= km; i++) at(j + i, c) -= at(j + i, j) * u;
+        }
+    }
+    for (size_t j = 0; j < n; j++) { /* L y = P b */
+        if (ipiv[j] != j) std::swap(b[j], b[ipiv[j]]);
+        const size_t km = std::min(kl, n - 1 - j);
+        const LD bj = b[j];
+        if (bj != 0.0L) for (size_t i = 1; i <= km; i++) b[j + i] -= at(j + i, j) * bj;
+    }
+    for (size_t j = n; j-- > 0;) { /* U x = y */
+        b[j] /= at(j, j);
+        const LD bj = b[j];
+        const size_t lo = j > kv ? j - kv : 0;
+        if (bj != 0.0L) for (size_t i = lo; i < j; i++) b[i] -= at(i, j) * bj;
+    }
+    return true;
+}
+
 // Least-squares / square solve by Householder QR with column pivoting (what RTR.colPivHouseholderQr().solve(ones) does in the
 // reference's Ng acceleration, lineProducingSpecies.tpp:300-302); rank decided with Eigen's default threshold n * epsilon.
 inline VecLD colpiv_qr_solve(std::vector<LD> A, VecLD b, const Size n) {
@@ -446,6 +486,12 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         VecLD y(n, 0.0L);
         std::vector<LD> scale(npoints);
         for (Size p = 0; p < npoints; p++) scale[p] = population_tot[p] > 0.0 ? (LD)population_tot[p] : 1.0L;
+        // per-unknown column scale: the level's current population (the solution is expected within a few orders of it), floored at
+        // 1e-60 of the point's total -- the Lambda elements of lines between nearly empty levels are huge numbers multiplying tiny ones
+        VecLD cscale(n);
+        for (Size p = 0; p < npoints; p++)
+            for (Size i = 0; i < nlev; i++)
+                cscale[(size_t)p * nlev + i] = std::max((LD)fabsl(population[index(p, i)]), 1.0e-60L * scale[p]);
         // ---- local parts of the blocks (radiative, collisional, conservation row), as in the block-diagonal path ----
 #pragma omp parallel
         {
@@ -502,8 +548,9 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         // ---- unknowns as fractions of the point's total: column scaling of every block and off-block entry; right-hand side -> 1 ----
 #pragma omp parallel for schedule(static)
         for (Size p = 0; p < npoints; p++) {
-            for (size_t e = 0; e < B; e++) D[B * p + e] *= scale[p];
-            for (size_t e = o_off[p]; e < o_off[p + 1]; e++) offs[e].v *= scale[offs[e].nr];
+            for (Size r = 0; r < nlev; r++)
+                for (Size c = 0; c < nlev; c++) D[B * p + (size_t)r * nlev + c] *= cscale[(size_t)p * nlev + c];
+            for (size_t e = o_off[p]; e < o_off[p + 1]; e++) offs[e].v *= cscale[(size_t)offs[e].nr * nlev + offs[e].col];
         }
         std::vector<LD> Dm = D; /* the blocks themselves (matrix-vector products); D becomes their LU factors */
         bool failed = false;
@@ -543,9 +590,42 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         //      relative -- what a backward-stable direct solver delivers at omega ~ epsilon); the correction A d = r is solved by one
         //      GMRES(restart) cycle on the block-Jacobi preconditioned system. The blocks can be badly conditioned (a point collects the
         //      Lambda elements of every list that names it), which is why convergence is NOT judged on the preconditioned residual. ----
+        // ---- start of the refinement. When the lists only name points within a few indices of their own (1D models: the points are
+        //      ordered along the radius and a ray couples a shell to its n_off_diag neighbours on either side) the system is a narrow
+        //      band matrix and a direct band LU with partial pivoting gives the solution outright; otherwise (3D point clouds: any
+        //      ordering leaves a wide band) the block-diagonal solution starts the Krylov refinement. ----
+        size_t pband = 0;
+        for (Size p = 0; p < npoints; p++)
+            for (size_t e = o_off[p]; e < o_off[p + 1]; e++) pband = std::max<size_t>(pband, offs[e].nr > p ? offs[e].nr - p : p - offs[e].nr);
+        const size_t kl = (pband + 1) * nlev - 1;
+        const char* want = getenv("MGBH_STATEQ_SOLVER"); /* "direct" | "krylov": tests */
+        const bool direct = want ? std::string(want) == "direct" : ((pband + 1) * nlev <= 512 && (3 * kl + 1) * n * sizeof(LD) <= (4ull << 30));
         VecLD f = y;
-        precond(f); /* start: the block-diagonal solution */
+        if (direct) {
+            const size_t ldab = 3 * kl + 1, kv = 2 * kl;
+            std::vector<LD> AB(ldab * n, 0.0L);
+            for (Size p = 0; p < npoints; p++) {
+                for (Size r = 0; r < nlev; r++)
+                    for (Size c = 0; c < nlev; c++) {
+                        const size_t i = (size_t)p * nlev + r, j = (size_t)p * nlev + c;
+                        AB[(kv + i - j) + ldab * j] = Dm[B * p + (size_t)r * nlev + c];
+                    }
+                for (size_t e = o_off[p]; e < o_off[p + 1]; e++) {
+                    const size_t i = (size_t)p * nlev + offs[e].row, j = (size_t)offs[e].nr * nlev + offs[e].col;
+                    AB[(kv + i - j) + ldab * j] += offs[e].v;
+                }
+            }
+            if (!band_lu_solve(AB, n, kl, kl, f)) throw std::runtime_error("Eigen solver ERROR.");
+        } else {
+            precond(f); /* the block-diagonal solution */
+        }
         VecLD r(n), w(n), mag(n);
+        if (getenv("MGBH_STATEQ_DEBUG")) {
+            LD fmax = 0.0L; size_t bad = 0, where = 0;
+            for (size_t i = 0; i < n; i++) { if (!std::isfinite((double)f[i])) bad++; else if (fabsl(f[i]) > fmax) { fmax = fabsl(f[i]); where = i; } }
+            LD omax = 0.0L; for (const auto& o : offs) omax = std::max(omax, fabsl(o.v));
+            fprintf(stderr, "[stateq] %s start (point band %zu): max |f| %.3Le at point %zu level %zu, %zu non-finite; %zu off-block entries, largest %.3Le\n", direct ? "direct band LU" : "block-diagonal", pband, fmax, where / nlev, where % nlev, bad, offs.size(), omax);
+        }
         const int restart = 40, max_outer = 80;
         const LD eps = std::numeric_limits<LD>::epsilon(), tol = 8.0L * eps;
         std::vector<VecLD> V;
@@ -559,11 +639,13 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
         for (int outer = 0; outer <= max_outer; outer++) {
             applyA(f, w, &mag);
             omega = 0.0L;
+            size_t worst_row = 0;
             for (size_t i = 0; i < n; i++) {
                 r[i] = y[i] - w[i];
                 const LD den = mag[i] + fabsl(y[i]);
-                if (r[i] != 0.0L) omega = std::max(omega, den > 0.0L ? fabsl(r[i]) / den : std::numeric_limits<LD>::infinity());
+                if (r[i] != 0.0L) { const LD o_i = den > 0.0L ? fabsl(r[i]) / den : std::numeric_limits<LD>::infinity(); if (o_i > omega) { omega = o_i; worst_row = i; } }
             }
+            if (debug) fprintf(stderr, "[stateq]   worst row: point %zu level %zu, y %.3Le, (|A||f|) %.3Le, r %.3Le\n", worst_row / nlev, worst_row % nlev, y[worst_row], mag[worst_row], r[worst_row]);
             if (debug) fprintf(stderr, "[stateq] refinement step %d, Krylov iterations %d, backward error %.3Le\n", outer, stateq_iterations, omega);
             if (omega < best) { best = omega; fbest = f; since_best = 0; } else since_best++;
             if (best <= tol || outer == max_outer || since_best >= 3) break;
@@ -583,7 +665,9 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
                     for (int i = 0; i <= j; i++) {
                         const LD h = dotp(w, V[i]);
                         if (pass == 0) H[i][j] = h; else H[i][j] += h;
-                        for (size_t q = 0; q < n; q++) w[q] -= h * V[i][q];
+                        const LD* vi = V[i].data();
+#pragma omp parallel for schedule(static)
+                        for (size_t q = 0; q < n; q++) w[q] -= h * vi[q];
                     }
                 H[j + 1][j] = sqrtl(dotp(w, w));
                 for (int i = 0; i < j; i++) { /* the previous Givens rotations on the new column */
@@ -602,21 +686,31 @@ struct LineProducingSpecies { // reference lineProducingSpecies.hpp / .tpp
                 H[j + 1][j] = 0.0L;
                 if (breakdown || fabsl(g[j + 1]) <= 1.0e-10L * beta) { j++; break; }
             }
+            if (debug) fprintf(stderr, "[stateq]   GMRES cycle: %d iterations, preconditioned residual reduced to %.3Le of its start\n", j, fabsl(g[j]) / beta);
             std::vector<LD> yk(j, 0.0L);
             for (int i = j; i-- > 0;) {
                 LD t = g[i];
                 for (int k = i + 1; k < j; k++) t -= H[i][k] * yk[k];
                 yk[i] = t / H[i][i];
             }
-            for (int i = 0; i < j; i++)
-                for (size_t q = 0; q < n; q++) f[q] += yk[i] * V[i][q];
+            for (int i = 0; i < j; i++) {
+                const LD c = yk[i];
+                const LD* vi = V[i].data();
+#pragma omp parallel for schedule(static)
+                for (size_t q = 0; q < n; q++) f[q] += c * vi[q];
+            }
         }
         if (!fbest.empty()) f.swap(fbest);
         stateq_residual = best;
-        if (!(best <= 1.0e-15L))
-            throw std::runtime_error("Eigen solver ERROR."); /* the banded system did not converge */
+        if (!(best <= 1.0e-15L)) {
+            char msg[400];
+            snprintf(msg, sizeof msg, "Eigen solver ERROR. (banded Lambda operator: the statistical-equilibrium system of %zu unknowns did not converge, "
+                     "backward error %.2Le after %d Krylov iterations; the block-Jacobi preconditioned refinement needs blocks that are regular on "
+                     "their own -- n_off_diag = 0 or a 1D model, which is solved directly, always works)", n, best, stateq_iterations);
+            throw std::runtime_error(msg); /* the text starts like lineProducingSpecies.tpp:551 */
+        }
         for (Size p = 0; p < npoints; p++)
-            for (Size i = 0; i < nlev; i++) population[index(p, i)] = f[(size_t)p * nlev + i] * scale[p];
+            for (Size i = 0; i < nlev; i++) population[index(p, i)] = f[(size_t)p * nlev + i] * cscale[(size_t)p * nlev + i];
     }
     // lineProducingSpecies.tpp:711-802
     void correct_negative_populations(const std::vector<Real>& temperature) {

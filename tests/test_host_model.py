@@ -76,12 +76,18 @@ def test_stateq_step_on_reference_radiation_field(name):
 BANDED = ["c1_all_constant", "c2_vanzadelhoff", "wind3d_small", "wind3d_spiral_2spec"]
 
 
-@pytest.mark.parametrize("name", BANDED)
-def test_banded_stateq_step_on_reference_radiation_field(name):
+@pytest.mark.parametrize("name,solver", [(n, s) for n in BANDED for s in ("direct", "krylov", None)
+                                         if not (s == "direct" and n.startswith("wind3d"))])
+def test_banded_stateq_step_on_reference_radiation_field(name, solver, monkeypatch):
     """n_off_diag > 0: compute_Jeff over the whole Lambda lists (bit-exact) and the GLOBAL statistical-equilibrium system (blocks +
-    off-block Lambda elements, block-Jacobi preconditioned GMRES in long double here, Eigen::SparseLU in the reference) on the J and
-    the lists of the reference's first iteration (tests/golden/offdiag_*.npz, offdiag_levelpop_*.npz)."""
+    off-block Lambda elements; Eigen::SparseLU in the reference) on the J and the lists of the reference's first iteration
+    (tests/golden/offdiag_*.npz, offdiag_levelpop_*.npz). Both host solvers: the direct band LU (what 1D models get) and the
+    block-Jacobi preconditioned GMRES refinement (what 3D point clouds get); solver = None is the automatic choice."""
     from magritte_b200 import model as hm
+    if solver:
+        monkeypatch.setenv("MGBH_STATEQ_SOLVER", solver)
+    else:
+        monkeypatch.delenv("MGBH_STATEQ_SOLVER", raising=False)
     flat, lists = util.load_golden_offdiag(name)
     lp = load_levelpop(name)
     gold = np.load(os.path.join(util.GOLDEN, f"offdiag_levelpop_{name}.npz"))
@@ -105,7 +111,10 @@ def test_banded_stateq_step_on_reference_radiation_field(name):
         fnc, mean, mx = m.convergence(l)
         assert abs(mx - gold["iter1_error_max"][l]) <= 1e-9 * max(1.0, abs(mx))
         assert abs(mean - gold["iter1_error_mean"][l]) <= 1e-9 * max(1.0, abs(mean))
-    assert coupled or name == "c1_all_constant", "the off-diagonal elements never entered the solve"
+    if solver == "krylov" and name != "c1_all_constant":
+        assert coupled, "the off-diagonal elements never entered the solve"
+    if solver is None:
+        assert coupled == name.startswith("wind3d"), "1D models take the direct band LU, 3D clouds the Krylov refinement"
 
 
 @pytest.mark.parametrize("name", BANDED)
